@@ -1,0 +1,116 @@
+/* proton_b200 — C ABI of the B200-native HHO / cutHHO hot path.
+ *
+ * The reference (OmarDuran/ProtoN) is a header-only C++ template library with no FFI layer: its drivers call
+ * free functions per cell from a serial loop.  This ABI is what a binding for that path would bind instead:
+ * the same stages, batched over all cells of a Cartesian mesh strip and executed by hand-written sm_100a
+ * kernels.  Each entry point cites the reference interface it replaces (paths relative to the reference
+ * root).  All pointers are caller-owned HOST arrays unless a name ends in `_dev`.  Every call returns a
+ * pb_status; pb_last_error() gives the message.  A context is bound to one CUDA device and is
+ * thread-compatible (one thread at a time).  There is no CPU fallback: without a CUDA device
+ * pb_ctx_create fails with PB_ERR_CUDA.
+ */
+#ifndef PROTON_B200_H
+#define PROTON_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pb_ctx pb_ctx;
+
+typedef enum { PB_OK = 0, PB_ERR_INVALID = 1, PB_ERR_CUDA = 2, PB_ERR_STATE = 3, PB_ERR_UNSUPPORTED = 4 } pb_status;
+
+/* which integrate(msh, cl, deg) overload the mesh type selects (src/core/core_bits/quadratures.hpp:311-375
+ * for quad_mesh, :377-402 for poly_mesh / cuthho_poly_mesh) */
+typedef enum { PB_QUAD_TENSOR_GAUSS = 0, PB_QUAD_POLY_DUNAVANT = 1 } pb_quad_kind;
+/* make_hho_naive_stabilization (src/methods/hho_bits/hho.hpp:99-148), make_hho_fancy_stabilization
+ * (:155-237), make_hho_cut_stabilization (apps/cuthho/cuthho_square.cpp:566-621) */
+typedef enum { PB_STAB_NAIVE = 0, PB_STAB_FANCY = 1, PB_STAB_CUT = 2 } pb_stab_kind;
+/* plain HHO Poisson (apps/convergence_test, apps/obstacle) or fictitious-domain cutHHO
+ * (run_cuthho_fictdom, apps/cuthho/cuthho_square.cpp:806-1080) */
+typedef enum { PB_PROBLEM_HHO = 0, PB_PROBLEM_FICTDOM = 1 } pb_problem_kind;
+/* the point-wise host lambdas of the drivers, as device functors: rhs_fun / sol_fun / sol_grad of
+ * convergence_test.cpp:100-113 and cuthho_square.cpp:847-866 (SINSIN), obstacle.cpp:65-89 (OBSTACLE), the
+ * commented-out tanh problem of convergence_test.cpp:115-138 (TANH) */
+typedef enum { PB_FUN_SINSIN = 0, PB_FUN_OBSTACLE = 1, PB_FUN_TANH = 2 } pb_fun_kind;
+/* element_location, src/methods/cuthho_bits/cuthho_mesh.hpp:31-36 */
+typedef enum { PB_IN_NEGATIVE_SIDE = 0, PB_IN_POSITIVE_SIDE = 1, PB_ON_INTERFACE = 2, PB_UNDEF = 3 } pb_location;
+/* cg_exit_reason, src/core/core_bits/solver_cg.hpp:37-42 */
+typedef enum { PB_CG_CONVERGED = 0, PB_CG_DIVERGED = 1, PB_CG_MAX_ITER_REACHED = 2 } pb_cg_exit_reason;
+
+/* hho_degree_info(cd, fd) + the per-driver choices (src/core/core_bits/utils.hpp:62-111) */
+typedef struct {
+    int cell_degree, face_degree;      /* invalid pairs revert to equal order like the reference */
+    int stab_kind;                     /* pb_stab_kind */
+    int problem;                       /* pb_problem_kind */
+    int fun;                           /* pb_fun_kind: source term, Dirichlet / Nitsche data, exact solution */
+    int rhs_degree_increase;           /* `di` of make_rhs (utils.hpp:153-174); obstacle.cpp:102 uses 1 */
+    double eta;                        /* Nitsche penalty, cell_eta() = 5 (cuthho_square.cpp:301-306) */
+    int keep_local;                    /* 1: also keep oper / (data+stab) / rhs per cell for pb_get_local */
+} pb_assembly_params;
+
+/* cg_params (solver_cg.hpp:44-61) */
+typedef struct { double convergence_threshold, divergence_threshold; long long max_iter; int apply_preconditioner; } pb_cg_params;
+
+typedef struct { long long iterations; double relative_residual; int exit_reason; double seconds; } pb_cg_result;
+
+/* ---- context ---- */
+pb_status pb_ctx_create(int device, pb_ctx** ctx);
+pb_status pb_ctx_destroy(pb_ctx* ctx);
+const char* pb_last_error(const pb_ctx* ctx);      /* ctx may be NULL: message of the last failed create */
+int pb_abi_version(void);
+
+/* ---- mesh: quad_mesh<T>(mesh_init_params) / cuthho_poly_mesh<T>(mip), src/core/core_bits/basic_mesh.hpp:178-197,
+ * 230-298, 321-403.  The Cartesian generator's sorted cell / face arrays are closed forms (cell (i,j) = j*Nx+i;
+ * faces ordered by (ptid0, ptid1)), so only the point coordinates live in memory.  [row_begin,row_end) is the
+ * strip of cell rows this context owns (multi-GPU: one context per rank); 0,Ny = the whole mesh. ---- */
+pb_status pb_mesh_cartesian(pb_ctx* ctx, long long Nx, long long Ny, double min_x, double max_x, double min_y, double max_y,
+                            int quad_kind, long long row_begin, long long row_end);
+/* all (Nx+1)*(Ny+1) points, xy interleaved (msh.points); set = after move_nodes (cuthho_geom.hpp:466-543) */
+pb_status pb_mesh_get_points(pb_ctx* ctx, double* xy);
+pb_status pb_mesh_set_points(pb_ctx* ctx, const double* xy);
+/* offset(msh, fc) of the 4 faces of every cell, in faces(msh, cl) order (basic_geom.hpp:183-212), and the
+ * assembler's compress_table (hho.hpp:313-323; -1 for Dirichlet faces) — for binding-side checks */
+pb_status pb_mesh_cell_faces(pb_ctx* ctx, long long* face_ids4);
+pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table);
+
+/* ---- cutHHO user data produced by detect_node_position / detect_cut_faces / detect_cut_cells /
+ * refine_interface (cuthho_geom.hpp:118-161, 275-340, 609-673): node and face locations, face intersection
+ * points, cell locations, and per cut cell its interface polyline (iface_off has ncells+1 entries). ---- */
+pb_status pb_cut_upload(pb_ctx* ctx, const int* node_location, const int* face_location, const double* face_intersection_xy,
+                        const int* cell_location, const long long* iface_off, const double* iface_xy);
+/* the same preprocessing run on the device for the circle level set (cuthho_square.cpp:2030-2052) */
+pb_status pb_cut_preprocess_circle(pb_ctx* ctx, double radius, double cx, double cy, int refine_steps);
+
+/* ---- stages 1+2: the drivers' per-cell loop (make_hho_laplacian + make_hho_*_stabilization + make_rhs, then
+ * static condensation) and assembler.assemble()/finalize() (hho.hpp:344-406, 451-455) onto the condensed face
+ * system: row/column of face dof (f,a) = compress_table[f]*fbs + a. ---- */
+pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* params);
+pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long long* n_cells, long long* n_local);
+/* assembler.LHS / assembler.RHS of the condensed system, CSR with sorted columns */
+pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs);
+/* per-cell dense results, column-major like Eigen, for cells [cell_begin, cell_begin+count):
+ * what = 0: lc = gr.second + stab (n x n); 1: oper = gr.first ((rbs-1) x n, or rbs x n rows padded layout, see
+ * DESIGN.md); 2: cell rhs (cbs); 3: condensed block S (4fbs x 4fbs); 4: condensed rhs g (4fbs). 0-2 need keep_local. */
+pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, long long count, double* out);
+
+/* ---- stage 3: conjugated_gradient(A, b, x, cg_params) (solver_cg.hpp:63-144) on the condensed system ---- */
+pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* params, pb_cg_result* result);
+pb_status pb_get_face_solution(pb_ctx* ctx, double* x);
+pb_status pb_set_face_solution(pb_ctx* ctx, const double* x);
+/* back-substitution: the reference's FULL solution vector (cell dofs c*cbs+i, then face dofs
+ * cbs*ncells + compress[f]*fbs + a), hho.hpp:362-379 */
+pb_status pb_recover(pb_ctx* ctx, double* full_solution);
+/* error norms of the drivers: out[0..2] = sums of squares of convergence_test.cpp:254-306 (L2, mass-norm, energy)
+ * for PB_PROBLEM_HHO; out[0] = H1 error^2 of cuthho_square.cpp:1031-1050 for PB_PROBLEM_FICTDOM */
+pb_status pb_error_norms(pb_ctx* ctx, double out[3]);
+
+/* ---- measurement hooks (bench.py): device-side timing of the last pb_assemble / pb_pcg, milliseconds ---- */
+pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg);
+/* register-resident DFMA peak probe (FP64 roofline denominator), TFLOP/s */
+pb_status pb_probe_fp64_peak(pb_ctx* ctx, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -291,3 +291,8 @@ double orc_obstacle_error(void* h, int fd, const double* alpha) {
 void orc_cell_barycenters(void* h, double* xy) { auto& m = ((MeshH*)h)->m; for (size_t c = 0; c < m.cells.size(); c++) { Pt b = barycenter(m, m.cells[c]); xy[2 * c] = b.x; xy[2 * c + 1] = b.y; } }
 
 }  // extern "C"
+
+extern "C" void orc_mesh_set_points(void* h, const double* xy) {
+    auto& m = ((MeshH*)h)->m;
+    for (size_t i = 0; i < m.points.size(); i++) m.points[i] = Pt(xy[2 * i], xy[2 * i + 1]);
+}

@@ -1,0 +1,210 @@
+"""ctypes binding of include/proton_b200.h.  Names follow the reference's host API where one exists
+(mesh_init_params: basic_mesh.hpp:178-197; hho_degree_info: utils.hpp:62-111; cg_params: solver_cg.hpp:44-61)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+
+
+class ProtonError(RuntimeError):
+    pass
+
+
+class PB:
+    OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_UNSUPPORTED = range(5)
+    QUAD_TENSOR_GAUSS, QUAD_POLY_DUNAVANT = 0, 1
+    STAB_NAIVE, STAB_FANCY, STAB_CUT = 0, 1, 2
+    PROBLEM_HHO, PROBLEM_FICTDOM = 0, 1
+    FUN_SINSIN, FUN_OBSTACLE, FUN_TANH = 0, 1, 2
+    IN_NEGATIVE_SIDE, IN_POSITIVE_SIDE, ON_INTERFACE, UNDEF = 0, 1, 2, 3
+    CG_CONVERGED, CG_DIVERGED, CG_MAX_ITER_REACHED = 0, 1, 2
+    LOCAL_LC, LOCAL_OPER, LOCAL_RHS, LOCAL_SCHUR, LOCAL_SCHUR_RHS, LOCAL_REC_A, LOCAL_REC_B = range(7)
+
+
+class _AssemblyParams(C.Structure):
+    _fields_ = [("cell_degree", C.c_int), ("face_degree", C.c_int), ("stab_kind", C.c_int), ("problem", C.c_int), ("fun", C.c_int),
+                ("rhs_degree_increase", C.c_int), ("eta", C.c_double), ("keep_local", C.c_int)]
+
+
+class _CgParams(C.Structure):
+    _fields_ = [("convergence_threshold", C.c_double), ("divergence_threshold", C.c_double), ("max_iter", C.c_longlong),
+                ("apply_preconditioner", C.c_int)]
+
+
+class _CgResult(C.Structure):
+    _fields_ = [("iterations", C.c_longlong), ("relative_residual", C.c_double), ("exit_reason", C.c_int), ("seconds", C.c_double)]
+
+
+def lib_path():
+    return os.path.join(_HERE, "libproton_b200.so")
+
+
+def abi_symbols():
+    """Entry points declared in include/proton_b200.h (parsed from the header)."""
+    txt = open(os.path.join(_ROOT, "include", "proton_b200.h")).read()
+    return sorted(set(re.findall(r"\b(pb_[a-z0-9_]+)\s*\(", txt)))
+
+
+_lib = None
+
+
+def lib():
+    """Load libproton_b200.so.  Fails loudly if the CUDA extension has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise ProtonError(f"{p} is missing: build it with `make -C proton_b200/csrc` (or __graft_entry__.build()); "
+                              "proton_b200 has no CPU fallback")
+        L = C.CDLL(p)
+        L.pb_last_error.restype = C.c_char_p
+        L.pb_last_error.argtypes = [C.c_void_p]
+        L.pb_mesh_cartesian.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
+                                        C.c_longlong, C.c_longlong]
+        L.pb_get_local.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+class mesh_init_params:
+    def __init__(self, Nx=4, Ny=4, min_x=0.0, max_x=1.0, min_y=0.0, max_y=1.0):
+        self.Nx, self.Ny, self.min_x, self.max_x, self.min_y, self.max_y = Nx, Ny, min_x, max_x, min_y, max_y
+
+
+class hho_degree_info:
+    def __init__(self, cd, fd=None):
+        if fd is None:
+            cd, fd = cd, cd
+        c1 = fd > 0 and cd in (fd - 1, fd, fd + 1)
+        c2 = fd == 0 and cd in (fd, fd + 1)
+        if not (c1 or c2):
+            cd = fd
+        self.cd, self.fd, self.rd = cd, fd, fd + 1
+
+    def cell_degree(self): return self.cd
+    def face_degree(self): return self.fd
+    def reconstruction_degree(self): return self.rd
+    @property
+    def cbs(self): return (self.cd + 1) * (self.cd + 2) // 2
+    @property
+    def fbs(self): return self.fd + 1
+    @property
+    def rbs(self): return (self.rd + 1) * (self.rd + 2) // 2
+
+
+class cg_params:
+    def __init__(self, convergence_threshold=1e-9, divergence_threshold=100.0, max_iter=1000, apply_preconditioner=False):
+        self.convergence_threshold, self.divergence_threshold = convergence_threshold, divergence_threshold
+        self.max_iter, self.apply_preconditioner = max_iter, apply_preconditioner
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One pb_ctx: a Cartesian mesh strip on one CUDA device and the condensed system assembled on it."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        rc = lib().pb_ctx_create(int(device), C.byref(self._h))
+        if rc != PB.OK:
+            raise ProtonError(lib().pb_last_error(None).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().pb_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != PB.OK:
+            raise ProtonError(f"[{rc}] " + lib().pb_last_error(self._h).decode())
+
+    # ---- mesh
+    def mesh(self, mip, quad_kind=PB.QUAD_TENSOR_GAUSS, row_begin=0, row_end=None):
+        row_end = mip.Ny if row_end is None else row_end
+        self._ck(lib().pb_mesh_cartesian(self._h, mip.Nx, mip.Ny, mip.min_x, mip.max_x, mip.min_y, mip.max_y, quad_kind, row_begin, row_end))
+        self.mip, self.quad_kind = mip, quad_kind
+        self.npoints = (mip.Nx + 1) * (mip.Ny + 1)
+        self.nfaces = 2 * mip.Nx * mip.Ny + mip.Nx + mip.Ny
+        self.ncells = mip.Nx * mip.Ny
+        return self
+
+    def points(self):
+        xy = np.zeros((self.npoints, 2)); self._ck(lib().pb_mesh_get_points(self._h, _ptr(xy))); return xy
+
+    def set_points(self, xy):
+        xy = np.ascontiguousarray(xy, np.float64); assert xy.shape == (self.npoints, 2)
+        self._ck(lib().pb_mesh_set_points(self._h, _ptr(xy)))
+
+    def cell_faces(self):
+        f = np.zeros((self.ncells, 4), np.int64); self._ck(lib().pb_mesh_cell_faces(self._h, _ptr(f))); return f
+
+    def compress_table(self):
+        t = np.zeros(self.nfaces, np.int64); self._ck(lib().pb_mesh_compress_table(self._h, _ptr(t))); return t
+
+    def cut_upload(self, node_loc, face_loc, face_ip, cell_loc, iface_off, iface_pts):
+        a = [np.ascontiguousarray(node_loc, np.int32), np.ascontiguousarray(face_loc, np.int32), np.ascontiguousarray(face_ip, np.float64),
+             np.ascontiguousarray(cell_loc, np.int32), np.ascontiguousarray(iface_off, np.int64), np.ascontiguousarray(iface_pts, np.float64)]
+        self._ck(lib().pb_cut_upload(self._h, *[_ptr(x) for x in a]))
+
+    # ---- stages 1+2
+    def assemble(self, hdi, stab_kind=PB.STAB_FANCY, problem=PB.PROBLEM_HHO, fun=PB.FUN_SINSIN, rhs_degree_increase=0, eta=5.0, keep_local=False):
+        p = _AssemblyParams(hdi.cd, hdi.fd, stab_kind, problem, fun, rhs_degree_increase, eta, int(keep_local))
+        self._ck(lib().pb_assemble(self._h, C.byref(p)))
+        self.hdi = hdi
+        n = C.c_longlong(); nnz = C.c_longlong(); nc = C.c_longlong(); nl = C.c_longlong()
+        self._ck(lib().pb_system_sizes(self._h, C.byref(n), C.byref(nnz), C.byref(nc), C.byref(nl)))
+        self.n_rows, self.nnz, self.ncells_local, self.n_local = n.value, nnz.value, nc.value, nl.value
+        return self
+
+    def csr(self, values=True):
+        rp = np.zeros(self.n_rows + 1, np.int64); col = np.zeros(self.nnz, np.int32)
+        val = np.zeros(self.nnz) if values else None; rhs = np.zeros(self.n_rows)
+        self._ck(lib().pb_get_csr(self._h, _ptr(rp), _ptr(col), _ptr(val), _ptr(rhs)))
+        return rp, col, val, rhs
+
+    def local(self, what, cell_begin=0, count=None):
+        count = self.ncells_local - cell_begin if count is None else count
+        h = self.hdi; nf = 4 * h.fbs; n = h.cbs + nf
+        shape = {PB.LOCAL_LC: (n, n), PB.LOCAL_OPER: (n, h.rbs), PB.LOCAL_RHS: (h.cbs,), PB.LOCAL_SCHUR: (nf, nf), PB.LOCAL_SCHUR_RHS: (nf,),
+                 PB.LOCAL_REC_A: (nf, h.cbs), PB.LOCAL_REC_B: (h.cbs,)}[what]
+        out = np.zeros((count,) + shape)
+        self._ck(lib().pb_get_local(self._h, what, cell_begin, count, _ptr(out)))
+        # device layout is column-major: out[c, col, row]; return [c, row, col]
+        return out.transpose(0, 2, 1).copy() if len(shape) == 2 else out
+
+    def timings(self):
+        a = C.c_double(); b = C.c_double(); c = C.c_double()
+        self._ck(lib().pb_last_timings(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(ms_local=a.value, ms_scatter=b.value, ms_pcg=c.value)
+
+    # ---- stage 3
+    def conjugated_gradient(self, cgp=None):
+        cgp = cgp or cg_params()
+        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(bool(cgp.apply_preconditioner)))
+        r = _CgResult()
+        self._ck(lib().pb_pcg(self._h, C.byref(p), C.byref(r)))
+        return dict(iterations=r.iterations, relative_residual=r.relative_residual, exit_reason=r.exit_reason, seconds=r.seconds)
+
+    def face_solution(self):
+        x = np.zeros(self.n_rows); self._ck(lib().pb_get_face_solution(self._h, _ptr(x))); return x
+
+    def set_face_solution(self, x):
+        x = np.ascontiguousarray(x, np.float64); assert x.shape == (self.n_rows,)
+        self._ck(lib().pb_set_face_solution(self._h, _ptr(x)))
+
+    def recover(self):
+        full = np.zeros(self.ncells * self.hdi.cbs + self.n_rows); self._ck(lib().pb_recover(self._h, _ptr(full))); return full
+
+    def error_norms(self):
+        out = np.zeros(3); self._ck(lib().pb_error_norms(self._h, _ptr(out))); return out
+
+    def probe_fp64_peak(self):
+        t = C.c_double(); self._ck(lib().pb_probe_fp64_peak(self._h, C.byref(t))); return t.value

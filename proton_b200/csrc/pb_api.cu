@@ -1,0 +1,572 @@
+// C ABI of proton_b200 (include/proton_b200.h): context, mesh, dispatch of the hand-written sm_100a kernels.
+#include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pb_local.cuh"
+#include "pb_pcg.cuh"
+#include "pb_system.cuh"
+
+using namespace pb;
+
+static std::string g_create_error;
+
+struct pb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // mesh
+    bool have_mesh = false;
+    Grid grid{}; Strip strip{}; int quad_kind = 0;
+    long long npoints = 0, ncells_local = 0, ncells_global = 0;
+    double2* points = nullptr;
+    int* cell_loc = nullptr;              // local cells
+    // assembly
+    bool assembled = false;
+    pb_assembly_params prm{};
+    int CD = 0, FD = 0, C = 0, F = 0, R = 0, N = 0, NF = 0;
+    double *S = nullptr, *g = nullptr, *recA = nullptr, *recb = nullptr, *lc = nullptr, *oper = nullptr, *rhsloc = nullptr;
+    long long nrows_blk = 0, nrows = 0, nnz = 0;
+    BlockRow* brows = nullptr; long long* brp = nullptr;
+    long long* rowptr = nullptr; int* col = nullptr; double *val = nullptr, *rhs = nullptr;
+    // solver
+    double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *parts = nullptr;
+    CgState* cg = nullptr;
+    // timings
+    cudaEvent_t ev[4]{};
+    double ms_local = 0, ms_scatter = 0, ms_pcg = 0;
+    size_t alloc_bytes = 0;
+};
+
+static pb_status fail(pb_ctx* c, pb_status st, const char* fmt, ...) {
+    char buf[512]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return st;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define NEED(cond, st, msg) do { if (!(cond)) return fail(ctx, st, "%s", msg); } while (0)
+
+template <typename T> static cudaError_t dalloc(pb_ctx* c, T** p, size_t n) {
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    if (n == 0) n = 1;
+    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+    if (e == cudaSuccess) c->alloc_bytes += n * sizeof(T);
+    return e;
+}
+template <typename T> static void dfree(T** p) { if (*p) cudaFree(*p); *p = nullptr; }
+
+// Gauss-Legendre closed forms in the reference's node order (quadratures.hpp:96-150) and the Dunavant rows
+// (quadratures_dunavant.hpp:27-118; published constants, stored as symmetry orbits and expanded in the reference order)
+static void fill_quad_tables(QuadTables& t) {
+    memset(&t, 0, sizeof t);
+    t.gx[1][0] = 0.0; t.gw[1][0] = 2.0;
+    { double q = 1.0 / std::sqrt(3.0); t.gx[2][0] = -q; t.gx[2][1] = q; t.gw[2][0] = t.gw[2][1] = 1.0; }
+    { double q = std::sqrt(3.0 / 5.0); t.gx[3][0] = -q; t.gx[3][1] = q; t.gx[3][2] = 0.0; t.gw[3][0] = t.gw[3][1] = 5.0 / 9.0; t.gw[3][2] = 8.0 / 9.0; }
+    { double a1 = 3.0 / 7.0, a2 = 2.0 * std::sqrt(6.0 / 5.0) / 7.0;
+      double q = std::sqrt(a1 - a2), w = (18.0 + std::sqrt(30.0)) / 36.0; t.gx[4][0] = -q; t.gx[4][1] = q; t.gw[4][0] = t.gw[4][1] = w;
+      q = std::sqrt(a1 + a2); w = (18.0 - std::sqrt(30.0)) / 36.0; t.gx[4][2] = -q; t.gx[4][3] = q; t.gw[4][2] = t.gw[4][3] = w; }
+    { t.gx[5][0] = 0.0; t.gw[5][0] = 128.0 / 225.0;
+      double a1 = 5.0, a2 = 2.0 * std::sqrt(10.0 / 7.0);
+      double q = std::sqrt(a1 - a2) / 3.0, w = (322 + 13.0 * std::sqrt(70.0)) / 900.0; t.gx[5][1] = -q; t.gx[5][2] = q; t.gw[5][1] = t.gw[5][2] = w;
+      q = std::sqrt(a1 + a2) / 3.0; w = (322 - 13.0 * std::sqrt(70.0)) / 900.0; t.gx[5][3] = -q; t.gx[5][4] = q; t.gw[5][3] = t.gw[5][4] = w; }
+    struct Orb { int rule, kind; double a, b, c, w; };
+    static const Orb orbs[] = {
+        {0, 1, 0.333333333333333, 0, 0, 1.000000000000000},
+        {1, 3, 0.666666666666667, 0.166666666666667, 0, 0.333333333333333},
+        {2, 1, 0.333333333333333, 0, 0, -0.562500000000000}, {2, 3, 0.600000000000000, 0.200000000000000, 0, 0.520833333333333},
+        {3, 3, 0.108103018168070, 0.445948490915965, 0, 0.223381589678011}, {3, 3, 0.816847572980459, 0.091576213509771, 0, 0.109951743655322},
+        {4, 1, 0.333333333333333, 0, 0, 0.225000000000000}, {4, 3, 0.059715871789770, 0.470142064105115, 0, 0.132394152788506},
+        {4, 3, 0.797426985353087, 0.101286507323456, 0, 0.125939180544827},
+        {5, 3, 0.501426509658179, 0.249286745170910, 0, 0.116786275726379}, {5, 3, 0.873821971016996, 0.063089014491502, 0, 0.050844906370207},
+        {5, 6, 0.053145049844817, 0.310352451033784, 0.636502499121399, 0.082851075618374},
+        {6, 1, 0.333333333333333, 0, 0, -0.149570044467682}, {6, 3, 0.479308067841920, 0.260345966079040, 0, 0.175615257433208},
+        {6, 3, 0.869739794195568, 0.065130102902216, 0, 0.053347235608838},
+        {6, 6, 0.048690315425316, 0.312865496004874, 0.638444188569810, 0.077113760890257},
+        {7, 1, 0.333333333333333, 0, 0, 0.144315607677787}, {7, 3, 0.081414823414554, 0.459292588292723, 0, 0.095091634267285},
+        {7, 3, 0.658861384496480, 0.170569307751760, 0, 0.103217370534718}, {7, 3, 0.898905543365938, 0.050547228317031, 0, 0.032458497623198},
+        {7, 6, 0.008394777409958, 0.263112829634638, 0.728492392955404, 0.027230314174435},
+    };
+    for (const Orb& o : orbs) {
+        int& n = t.dun_n[o.rule];
+        auto put = [&](double l0, double l1, double l2) { double* r = t.dun[o.rule][n++]; r[0] = l0; r[1] = l1; r[2] = l2; r[3] = o.w; };
+        if (o.kind == 1) put(o.a, o.a, o.a);
+        else if (o.kind == 3) { put(o.a, o.b, o.b); put(o.b, o.a, o.b); put(o.b, o.b, o.a); }
+        else { put(o.a, o.b, o.c); put(o.a, o.c, o.b); put(o.b, o.a, o.c); put(o.b, o.c, o.a); put(o.c, o.a, o.b); put(o.c, o.b, o.a); }
+    }
+}
+
+extern "C" int pb_abi_version(void) { return 1; }
+
+extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
+    pb_ctx* ctx = nullptr;
+    if (!out) return fail(nullptr, PB_ERR_INVALID, "pb_ctx_create: null output pointer");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, PB_ERR_CUDA, "pb_ctx_create: no CUDA device (%s); proton_b200 has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (device < 0 || device >= ndev) return fail(nullptr, PB_ERR_INVALID, "pb_ctx_create: device %d out of range [0,%d)", device, ndev);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, PB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    ctx = new pb_ctx; ctx->device = device;
+    QuadTables t; fill_quad_tables(t);
+    if ((e = cudaMemcpyToSymbol(c_qt, &t, sizeof t)) != cudaSuccess || (e = cudaStreamCreate(&ctx->stream)) != cudaSuccess) {
+        pb_status st = fail(nullptr, PB_ERR_CUDA, "pb_ctx_create: %s", cudaGetErrorString(e)); delete ctx; return st;
+    }
+    for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    cudaMalloc((void**)&ctx->cg, sizeof(CgState));
+    *out = ctx; return PB_OK;
+}
+
+static void free_system(pb_ctx* c) {
+    dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
+    dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
+    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->d); dfree(&c->y); dfree(&c->iA); dfree(&c->parts);
+    c->assembled = false;
+}
+
+extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
+    if (!ctx) return PB_OK;
+    cudaSetDevice(ctx->device);
+    free_system(ctx); dfree(&ctx->points); dfree(&ctx->cell_loc); dfree(&ctx->cg);
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx; return PB_OK;
+}
+
+extern "C" const char* pb_last_error(const pb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+// ------------------------------------------------------------------------------------------------ mesh
+// points p(i,j) = (min_x + i*hx, min_y + j*hy) exactly as the host generator rounds them (basic_mesh.hpp:240-249):
+// product and sum rounded separately, no FMA contraction.
+__global__ void gen_points_kernel(Grid g, double2* pts) {
+    long long n = (g.Nx + 1) * (g.Ny + 1);
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        long long j = t / (g.Nx + 1), i = t - j * (g.Nx + 1);
+        pts[t] = make_double2(__dadd_rn(g.min_x, __dmul_rn((double)i, g.hx)), __dadd_rn(g.min_y, __dmul_rn((double)j, g.hy)));
+    }
+}
+
+extern "C" pb_status pb_mesh_cartesian(pb_ctx* ctx, long long Nx, long long Ny, double min_x, double max_x, double min_y, double max_y,
+                                       int quad_kind, long long row_begin, long long row_end) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(Nx >= 2 && Ny >= 2, PB_ERR_INVALID, "pb_mesh_cartesian: need Nx, Ny >= 2");
+    NEED(quad_kind == PB_QUAD_TENSOR_GAUSS || quad_kind == PB_QUAD_POLY_DUNAVANT, PB_ERR_INVALID, "pb_mesh_cartesian: bad quad_kind");
+    NEED(0 <= row_begin && row_begin < row_end && row_end <= Ny, PB_ERR_INVALID, "pb_mesh_cartesian: bad row range");
+    NEED((Nx + 1) * (Ny + 1) < (1LL << 31) && 4 * (2 * Nx * Ny) < (1LL << 31), PB_ERR_UNSUPPORTED, "pb_mesh_cartesian: mesh too large for 32-bit column indices");
+    CK(cudaSetDevice(ctx->device));
+    free_system(ctx);
+    Grid& g = ctx->grid;
+    g.Nx = Nx; g.Ny = Ny; g.row_begin = row_begin; g.row_end = row_end; g.min_x = min_x; g.min_y = min_y;
+    g.hx = (max_x - min_x) / Nx; g.hy = (max_y - min_y) / Ny;      // mesh_init_params::hx/hy, basic_mesh.hpp:190-196
+    ctx->quad_kind = quad_kind;
+    ctx->npoints = (Nx + 1) * (Ny + 1);
+    ctx->ncells_global = Nx * Ny;
+    // owned block rows: faces whose id lies in face-rows [row_begin, row_end): bottom and vertical faces of the owned
+    // cell rows.  The rows of the strip's bottom faces need the cell row below => one ghost row of cells.
+    Strip& s = ctx->strip;
+    s.cf_begin = compress_row_start(g, row_begin);
+    s.cf_end = row_end == Ny ? num_free_faces(g) : compress_row_start(g, row_end);
+    s.cell_row0 = row_begin > 0 ? row_begin - 1 : 0;
+    s.col_lo = compress_row_start(g, s.cell_row0);
+    s.col_hi = row_end == Ny ? num_free_faces(g) : compress_row_start(g, row_end) + (2 * Nx - 1);   // through the top faces h(.,row_end)
+    if (s.col_hi > num_free_faces(g)) s.col_hi = num_free_faces(g);
+    ctx->ncells_local = (row_end - s.cell_row0) * Nx;
+    CK(dalloc(ctx, &ctx->points, (size_t)ctx->npoints));
+    dfree(&ctx->cell_loc);
+    gen_points_kernel<<<148 * 4, 256, 0, ctx->stream>>>(g, ctx->points);
+    CK(cudaGetLastError()); CK(cudaStreamSynchronize(ctx->stream));
+    ctx->have_mesh = true; return PB_OK;
+}
+
+extern "C" pb_status pb_mesh_get_points(pb_ctx* ctx, double* xy) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && xy, PB_ERR_STATE, "pb_mesh_get_points: no mesh");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(xy, ctx->points, (size_t)ctx->npoints * 16, cudaMemcpyDeviceToHost)); return PB_OK;
+}
+extern "C" pb_status pb_mesh_set_points(pb_ctx* ctx, const double* xy) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && xy, PB_ERR_STATE, "pb_mesh_set_points: no mesh");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(ctx->points, xy, (size_t)ctx->npoints * 16, cudaMemcpyHostToDevice)); ctx->assembled = false; return PB_OK;
+}
+extern "C" pb_status pb_mesh_cell_faces(pb_ctx* ctx, long long* out) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && out, PB_ERR_STATE, "pb_mesh_cell_faces: no mesh");
+    const Grid& g = ctx->grid;
+    for (long long j = 0; j < g.Ny; j++) for (long long i = 0; i < g.Nx; i++) cell_faces(g, i, j, out + 4 * (j * g.Nx + i));
+    return PB_OK;
+}
+extern "C" pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && table, PB_ERR_STATE, "pb_mesh_compress_table: no mesh");
+    const Grid& g = ctx->grid;
+    long long nf = 2 * g.Nx * g.Ny + g.Nx + g.Ny;
+    for (long long f = 0; f < nf; f++) table[f] = -1;
+    for (long long j = 0; j < g.Ny; j++) for (long long i = 0; i < g.Nx; i++) {
+        long long f[4]; cell_faces(g, i, j, f);
+        for (int li = 0; li < 4; li++) if (!cell_face_dirichlet(g, i, j, li)) table[f[li]] = cell_face_compressed(g, i, j, li);
+    }
+    return PB_OK;
+}
+extern "C" pb_status pb_cut_upload(pb_ctx* ctx, const int*, const int*, const double*, const int* cell_location, const long long*, const double*) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && cell_location, PB_ERR_STATE, "pb_cut_upload: no mesh");
+    CK(cudaSetDevice(ctx->device));
+    CK(dalloc(ctx, &ctx->cell_loc, (size_t)ctx->ncells_local));
+    CK(cudaMemcpy(ctx->cell_loc, cell_location + ctx->strip.cell_row0 * ctx->grid.Nx, (size_t)ctx->ncells_local * 4, cudaMemcpyHostToDevice));
+    ctx->assembled = false;
+    return PB_OK;   // cut-cell payload is consumed by K2 (pb_local_cut.cuh) once uploaded; see DESIGN.md
+}
+extern "C" pb_status pb_cut_preprocess_circle(pb_ctx* ctx, double, double, double, int) {
+    if (!ctx) return PB_ERR_INVALID;
+    return fail(ctx, PB_ERR_UNSUPPORTED, "pb_cut_preprocess_circle: device-side preprocessing not built yet (SURVEY 8f.2)");
+}
+
+// ------------------------------------------------------------------------------------------------ stage 1+2
+template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB>
+static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A) {
+    constexpr int QC = cell_qps(QK, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
+    using SM = LocalSmem<CD, FD, QCMAX>;
+    const size_t smem = sizeof(SM) * (TPB / GS);
+    auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int bps = 0, nsm = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, TPB, smem)) != cudaSuccess) return e;
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+    if (bps < 1) return cudaErrorLaunchOutOfResources;
+    long long need = (A.ncells + (TPB / GS) - 1) / (TPB / GS), cap = (long long)nsm * bps;
+    int grid = (int)(need < cap ? need : cap);
+    kern<<<grid, TPB, smem, c->stream>>>(A);
+    return cudaGetLastError();
+}
+
+// (cell degree, face degree, quadrature kind, stabilisation, load quadrature degree) -> kernel instance
+static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd, int qk, int sk, int rqd, bool* found) {
+    *found = true;
+#define PB_CASE(CD_, FD_, QK_, SK_, RQD_, GS_, TPB_) \
+    if (cd == CD_ && fd == FD_ && qk == QK_ && sk == SK_ && rqd == RQD_) return launch_local<CD_, FD_, QK_, SK_, RQD_, GS_, TPB_>(c, A);
+    // HHO(k+1,k), tensor Gauss (convergence_test): fancy and naive
+    PB_CASE(1, 0, 0, 1, 2, 8, 256)  PB_CASE(1, 0, 0, 0, 2, 8, 256)
+    PB_CASE(2, 1, 0, 1, 4, 16, 256) PB_CASE(2, 1, 0, 0, 4, 16, 256)
+    PB_CASE(3, 2, 0, 1, 6, 32, 256) PB_CASE(3, 2, 0, 0, 6, 32, 256)
+    PB_CASE(4, 3, 0, 1, 8, 32, 128) PB_CASE(4, 3, 0, 0, 8, 32, 128)
+    // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive
+    PB_CASE(1, 0, 1, 0, 2, 8, 256)
+    PB_CASE(2, 1, 1, 0, 4, 16, 256)
+    PB_CASE(3, 2, 1, 0, 6, 32, 256)
+#undef PB_CASE
+    *found = false; return cudaSuccess;
+}
+
+static pb_status build_structure(pb_ctx* ctx) {
+    const long long nbr = ctx->strip.cf_end - ctx->strip.cf_begin;
+    const int F = ctx->F;
+    ctx->nrows_blk = nbr; ctx->nrows = nbr * F;
+    int* nb = nullptr;
+    CK(dalloc(ctx, &ctx->brows, (size_t)nbr)); CK(dalloc(ctx, &ctx->brp, (size_t)nbr + 1));
+    CK(cudaMalloc((void**)&nb, (size_t)(nbr + 1) * 4));
+    CK(cudaMemsetAsync(nb, 0, (size_t)(nbr + 1) * 4, ctx->stream));
+    build_block_rows_kernel<<<(unsigned)((nbr + 255) / 256), 256, 0, ctx->stream>>>(ctx->grid, ctx->strip, ctx->brows, nb);
+    CK(cudaGetLastError());
+    void* tmp = nullptr; size_t tmpb = 0;
+    // exclusive scan of nb (int) into brp (long long) over nbr+1 items (the extra 0 yields the total)
+    CK(cub::DeviceScan::ExclusiveScan(nullptr, tmpb, nb, ctx->brp, cuda::std::plus<>(), 0LL, (int)(nbr + 1), ctx->stream));
+    CK(cudaMalloc(&tmp, tmpb));
+    CK(cub::DeviceScan::ExclusiveScan(tmp, tmpb, nb, ctx->brp, cuda::std::plus<>(), 0LL, (int)(nbr + 1), ctx->stream));
+    long long nblk = 0;
+    CK(cudaMemcpyAsync(&nblk, ctx->brp + nbr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(tmp); cudaFree(nb);
+    ctx->nnz = nblk * F * F;
+    CK(dalloc(ctx, &ctx->rowptr, (size_t)ctx->nrows + 1)); CK(dalloc(ctx, &ctx->col, (size_t)ctx->nnz));
+    CK(dalloc(ctx, &ctx->val, (size_t)ctx->nnz)); CK(dalloc(ctx, &ctx->rhs, (size_t)ctx->nrows));
+    fill_csr_pattern_kernel<<<(unsigned)((ctx->nrows + 1 + 255) / 256), 256, 0, ctx->stream>>>(nbr, F, ctx->brows, ctx->brp, ctx->rowptr, ctx->col);
+    CK(cudaGetLastError());
+    return PB_OK;
+}
+
+extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && p, PB_ERR_STATE, "pb_assemble: no mesh");
+    CK(cudaSetDevice(ctx->device));
+    int cd = p->cell_degree, fd = p->face_degree;
+    NEED(cd >= 0 && fd >= 0, PB_ERR_INVALID, "pb_assemble: negative degree");
+    {   // hho_degree_info(cd, fd): invalid pairs revert to equal order (utils.hpp:75-95)
+        bool c1 = fd > 0 && (cd == fd - 1 || cd == fd || cd == fd + 1), c2 = fd == 0 && (cd == fd || cd == fd + 1);
+        if (!(c1 || c2)) cd = fd;
+    }
+    NEED(p->problem == PB_PROBLEM_HHO || p->problem == PB_PROBLEM_FICTDOM, PB_ERR_INVALID, "pb_assemble: bad problem kind");
+    if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->cell_loc != nullptr, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_upload first");
+    int sk = p->stab_kind == PB_STAB_FANCY ? 1 : 0;
+    const int rqd = 2 * (cd + p->rhs_degree_increase);
+    bool relayout = !ctx->assembled || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc);
+    ctx->prm = *p; ctx->CD = cd; ctx->FD = fd;
+    ctx->C = cell_basis_size(cd); ctx->F = fd + 1; ctx->R = cell_basis_size(fd + 1); ctx->NF = 4 * ctx->F; ctx->N = ctx->C + ctx->NF;
+    const long long nc = ctx->ncells_local;
+    if (relayout) {
+        free_system(ctx);
+        CK(dalloc(ctx, &ctx->S, (size_t)nc * ctx->NF * ctx->NF)); CK(dalloc(ctx, &ctx->g, (size_t)nc * ctx->NF));
+        CK(dalloc(ctx, &ctx->recA, (size_t)nc * ctx->NF * ctx->C)); CK(dalloc(ctx, &ctx->recb, (size_t)nc * ctx->C));
+        if (p->keep_local) {
+            CK(dalloc(ctx, &ctx->lc, (size_t)nc * ctx->N * ctx->N)); CK(dalloc(ctx, &ctx->oper, (size_t)nc * ctx->N * ctx->R));
+            CK(dalloc(ctx, &ctx->rhsloc, (size_t)nc * ctx->C));
+        }
+        pb_status st = build_structure(ctx); if (st != PB_OK) return st;
+    }
+    LocalArgs A{};
+    A.grid = ctx->grid; A.grid.row_begin = ctx->strip.cell_row0;      // local cell 0 sits in row cell_row0
+    A.points = ctx->points; A.cell_loc = p->problem == PB_PROBLEM_FICTDOM ? ctx->cell_loc : nullptr;
+    A.ncells = nc; A.fun = p->fun; A.problem = p->problem; A.eta = p->eta;
+    A.S = ctx->S; A.g = ctx->g; A.recA = ctx->recA; A.recb = ctx->recb;
+    A.lc = p->keep_local ? ctx->lc : nullptr; A.oper = p->keep_local ? ctx->oper : nullptr; A.rhs = p->keep_local ? ctx->rhsloc : nullptr;
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    bool found = false;
+    CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
+    if (!found) return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: no kernel instance for HHO(%d,%d) quad_kind=%d stab=%d load degree %d", cd, fd, ctx->quad_kind, p->stab_kind, rqd);
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    const int F = ctx->F;
+    scatter_values_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
+    CK(cudaGetLastError());
+    scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_local = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->ms_scatter = ms;
+    ctx->assembled = true;
+    return PB_OK;
+}
+
+extern "C" pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long long* n_cells, long long* n_local) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled, PB_ERR_STATE, "pb_system_sizes: nothing assembled");
+    if (n_rows) *n_rows = ctx->nrows; if (nnz) *nnz = ctx->nnz; if (n_cells) *n_cells = ctx->ncells_local; if (n_local) *n_local = ctx->N;
+    return PB_OK;
+}
+extern "C" pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled, PB_ERR_STATE, "pb_get_csr: nothing assembled");
+    CK(cudaSetDevice(ctx->device));
+    if (rowptr) CK(cudaMemcpy(rowptr, ctx->rowptr, (size_t)(ctx->nrows + 1) * 8, cudaMemcpyDeviceToHost));
+    if (col) CK(cudaMemcpy(col, ctx->col, (size_t)ctx->nnz * 4, cudaMemcpyDeviceToHost));
+    if (val) CK(cudaMemcpy(val, ctx->val, (size_t)ctx->nnz * 8, cudaMemcpyDeviceToHost));
+    if (rhs) CK(cudaMemcpy(rhs, ctx->rhs, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
+    return PB_OK;
+}
+extern "C" pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, long long count, double* out) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && out, PB_ERR_STATE, "pb_get_local: nothing assembled");
+    NEED(cell_begin >= 0 && count >= 0 && cell_begin + count <= ctx->ncells_local, PB_ERR_INVALID, "pb_get_local: cell range out of bounds");
+    const double* src = nullptr; long long per = 0;
+    switch (what) {
+    case 0: src = ctx->lc; per = (long long)ctx->N * ctx->N; break;
+    case 1: src = ctx->oper; per = (long long)ctx->N * ctx->R; break;
+    case 2: src = ctx->rhsloc; per = ctx->C; break;
+    case 3: src = ctx->S; per = (long long)ctx->NF * ctx->NF; break;
+    case 4: src = ctx->g; per = ctx->NF; break;
+    case 5: src = ctx->recA; per = (long long)ctx->NF * ctx->C; break;
+    case 6: src = ctx->recb; per = ctx->C; break;
+    default: return fail(ctx, PB_ERR_INVALID, "pb_get_local: unknown selector %d", what);
+    }
+    NEED(src != nullptr, PB_ERR_STATE, "pb_get_local: assemble with keep_local=1 to read lc/oper/rhs");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(out, src + cell_begin * per, (size_t)(count * per) * 8, cudaMemcpyDeviceToHost));
+    return PB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ stage 3
+static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 ? 8 : len <= 24 ? 8 : 16; }
+
+extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && p, PB_ERR_STATE, "pb_pcg: nothing assembled");
+    NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED,
+         "pb_pcg: this context owns a strip; the multi-rank solve is driven through pb_pcg_* step calls");
+    CK(cudaSetDevice(ctx->device));
+    const long long n = ctx->nrows;
+    if (!ctx->x) {
+        CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
+        CK(dalloc(ctx, &ctx->d, (size_t)n)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
+        CK(dalloc(ctx, &ctx->parts, (size_t)3 * PCG_MAX_BLOCKS));
+    }
+    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
+    int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
+    long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
+    double *p_dy = ctx->parts, *p_rr = ctx->parts + PCG_MAX_BLOCKS, *p_rz = ctx->parts + 2 * PCG_MAX_BLOCKS;
+    const int pre = p->apply_preconditioner ? 1 : 0;
+    const int lpr = spmv_lanes(ctx->F);
+    auto t0 = std::chrono::steady_clock::now();
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    pcg_diag_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
+    pcg_init_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
+    pcg_init_state_kernel<<<1, PCG_THREADS, 0, ctx->stream>>>(nblk, p_rr, p_rz, ctx->cg);
+    CK(cudaGetLastError());
+    CgState hs{}; long long it = 0; const long long check_every = 32;
+    while (true) {
+        for (long long k = 0; k < check_every; k++, it++) {
+            if (it > 0) {
+                pcg_dir_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, nblk, p_rr, p_rz, ctx->z, ctx->d, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+                pcg_commit_kernel<<<1, PCG_THREADS, 0, ctx->stream>>>(nblk, p_rr, p_rz, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+            }
+            switch (lpr) {
+            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
+            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
+            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
+            }
+            pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, pre, nblk, p_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
+        }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (hs.done) break;
+    }
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream)); CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
+    if (res) {
+        res->iterations = hs.iters; res->relative_residual = hs.relres; res->exit_reason = hs.reason;
+        res->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return PB_OK;
+}
+
+extern "C" pb_status pb_get_face_solution(pb_ctx* ctx, double* x) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && x, PB_ERR_STATE, "pb_get_face_solution: no solution");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(x, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost)); return PB_OK;
+}
+extern "C" pb_status pb_set_face_solution(pb_ctx* ctx, const double* x) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && x, PB_ERR_STATE, "pb_set_face_solution: nothing assembled");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->x) CK(dalloc(ctx, &ctx->x, (size_t)ctx->nrows));
+    CK(cudaMemcpy(ctx->x, x, (size_t)ctx->nrows * 8, cudaMemcpyHostToDevice)); return PB_OK;
+}
+
+// K6 — back-substitution u_T = K_TT^{-1} f_T - (K_TT^{-1} K_TF) u_F with the Dirichlet face values re-projected
+// (take_local_data, hho.hpp:408-449).  One thread per cell.
+template <int FD>
+__global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, long long row_first_owned, int C, int fun, const double2* __restrict__ points,
+                               const double* __restrict__ recA, const double* __restrict__ recb, const double* __restrict__ xf, long long xoff,
+                               double* __restrict__ ucell) {
+    constexpr int F = FD + 1, NF = 4 * F, QF = FD + 1;
+    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x) {
+        long long ci = c % g.Nx, cj = cell_row0 + c / g.Nx;
+        if (cj < row_first_owned) continue;                 // ghost row: recovered by its owner
+        double uF[NF];
+        CellGeom geo;
+        long long p0 = grid_point(g, ci, cj);
+        double2 a = points[p0], b = points[p0 + 1], cc = points[p0 + g.Nx + 2], d = points[p0 + g.Nx + 1];
+        geo.vx[0] = a.x; geo.vy[0] = a.y; geo.vx[1] = b.x; geo.vy[1] = b.y; geo.vx[2] = cc.x; geo.vy[2] = cc.y; geo.vx[3] = d.x; geo.vy[3] = d.y;
+#pragma unroll
+        for (int li = 0; li < 4; li++) {
+            if (!cell_face_dirichlet(g, ci, cj, li)) {
+                long long cf = cell_face_compressed(g, ci, cj, li);
+#pragma unroll
+                for (int k = 0; k < F; k++) uF[li * F + k] = xf[cf * F + k - xoff];
+            } else {
+                double ax, ay, bx, by; face_points(geo, li, ax, ay, bx, by);
+                double len = sqrt((bx - ax) * (bx - ax) + (by - ay) * (by - ay)), fbx = 0.5 * (ax + bx), fby = 0.5 * (ay + by);
+                double Mf[F * (F + 1) / 2], gd[F];
+#pragma unroll
+                for (int k = 0; k < F * (F + 1) / 2; k++) Mf[k] = 0.0;
+#pragma unroll
+                for (int k = 0; k < F; k++) gd[k] = 0.0;
+#pragma unroll
+                for (int q = 0; q < QF; q++) {
+                    double t = c_qt.gx[QF][q], px = 0.5 * (1 - t) * ax + 0.5 * (1 + t) * bx, py = 0.5 * (1 - t) * ay + 0.5 * (1 + t) * by;
+                    double w = c_qt.gw[QF][q] * len * 0.5;
+                    double ep = 4.0 * ((fbx - ax) * (px - fbx) + (fby - ay) * (py - fby)) / (len * len);
+                    double ph[F]; ph[0] = 1.0;
+#pragma unroll
+                    for (int k = 1; k < F; k++) ph[k] = ph[k - 1] * ep;
+                    double bc = fun_sol(fun, px, py);
+#pragma unroll
+                    for (int k = 0; k < F; k++) {
+                        gd[k] += w * ph[k] * bc;
+#pragma unroll
+                        for (int m = 0; m <= k; m++) Mf[PB_TRI(k, m)] += w * ph[k] * ph[m];
+                    }
+                }
+                ldlt_packed<F>(Mf); ldlt_solve<F>(Mf, gd);
+#pragma unroll
+                for (int k = 0; k < F; k++) uF[li * F + k] = gd[k];
+            }
+        }
+        long long gc = cj * g.Nx + ci;
+        for (int k = 0; k < C; k++) {
+            double v = recb[c * C + k];
+#pragma unroll
+            for (int i = 0; i < NF; i++) v -= recA[(c * NF + i) * C + k] * uF[i];
+            ucell[gc * C + k] = v;
+        }
+    }
+}
+
+extern "C" pb_status pb_recover(pb_ctx* ctx, double* full) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && full, PB_ERR_STATE, "pb_recover: no face solution");
+    NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_recover: whole-mesh contexts only");
+    CK(cudaSetDevice(ctx->device));
+    const long long ncg = ctx->ncells_global; const int C = ctx->C;
+    double* uc = nullptr; CK(cudaMalloc((void**)&uc, (size_t)ncg * C * 8));
+#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(ctx->grid, ctx->strip.cell_row0, ctx->ncells_local, ctx->grid.row_begin, C, ctx->prm.fun, \
+        ctx->points, ctx->recA, ctx->recb, ctx->x, 0, uc)
+    switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; case 2: PB_REC(2); break; case 3: PB_REC(3); break;
+    default: cudaFree(uc); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_recover: face degree %d", ctx->FD); }
+#undef PB_REC
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(full, uc, (size_t)ncg * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(full + ncg * C, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(uc);
+    return PB_OK;
+}
+
+extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
+    if (!ctx) return PB_ERR_INVALID;
+    (void)out;
+    return fail(ctx, PB_ERR_UNSUPPORTED, "pb_error_norms: not built yet (SURVEY 8f.1)");
+}
+
+extern "C" pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg) {
+    if (!ctx) return PB_ERR_INVALID;
+    if (ms_local) *ms_local = ctx->ms_local; if (ms_scatter) *ms_scatter = ctx->ms_scatter; if (ms_pcg) *ms_pcg = ctx->ms_pcg;
+    return PB_OK;
+}
+
+// register-resident DFMA chains: 8 independent accumulators per thread, 2 flop per FMA
+__global__ void fp64_probe_kernel(double* out, int iters, double a, double b) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+        x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+        x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+    out[blockIdx.x * (size_t)blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+extern "C" pb_status pb_probe_fp64_peak(pb_ctx* ctx, double* tflops) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(tflops, PB_ERR_INVALID, "pb_probe_fp64_peak: null output");
+    CK(cudaSetDevice(ctx->device));
+    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
+    const int blocks = nsm * 8, threads = 256, iters = 1 << 16;
+    double* out = nullptr; CK(cudaMalloc((void**)&out, (size_t)blocks * threads * 8));
+    double best = 0;
+    for (int rep = 0; rep < 4; rep++) {
+        CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+        fp64_probe_kernel<<<blocks, threads, 0, ctx->stream>>>(out, iters, 0.999999, 1e-7);
+        CK(cudaEventRecord(ctx->ev[1], ctx->stream)); CK(cudaStreamSynchronize(ctx->stream));
+        float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+        double tf = 2.0 * 8 * (double)iters * blocks * threads / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaFree(out); *tflops = best; return PB_OK;
+}

@@ -1,0 +1,165 @@
+// K4/K5 — Jacobi-preconditioned conjugate gradient on the condensed face system: the reference's
+// conjugated_gradient (solver_cg.hpp:63-144) with the same update order, stopping tests and iteration count,
+// as three bandwidth-bound kernels per iteration:
+//   dir   : [reduce (r.r, r.z)] -> exit tests -> beta -> d = z + beta d            (iteration > 0)
+//   spmv  : y = A d  fused with the partial sums of d.y
+//   xrz   : [reduce d.y] -> alpha -> x += alpha d, r -= alpha y, z = M^{-1} r, partial sums of r.r and r.z
+// Reductions are two-stage (per-block partials, then every block re-reduces the same partial array in the same
+// order), so results are deterministic and no host round trip is needed inside an iteration.
+#pragma once
+#include "pb_device.cuh"
+
+namespace pb {
+
+struct CgState {               // lives in device memory
+    double rho;                // r . M^{-1} r of the current residual
+    double nr0;                // ||r0||
+    double relres;             // nr / nr0 at exit
+    long long iters;           // completed direction updates at exit (solver_cg.hpp `iter`)
+    int done, reason;
+};
+
+constexpr int PCG_THREADS = 256;
+constexpr int PCG_MAX_BLOCKS = 148 * 8;     // persistent grid: multiple of the SM count
+
+PB_D double block_reduce_sum(double v, double* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (threadIdx.x < 32) {
+        t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    }
+    __syncthreads();
+    return t;    // valid in thread 0
+}
+// every block sums the same nparts partials in the same order -> identical result everywhere
+PB_D double reduce_partials(const double* parts, int nparts, double* sh) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) v += parts[i];
+    double t = block_reduce_sum(v, sh);
+    __shared__ double bc;
+    if (threadIdx.x == 0) bc = t;
+    __syncthreads();
+    double r = bc;
+    __syncthreads();
+    return r;
+}
+
+// iA = 1/diag(A) (solver_cg.hpp:78-81); A is scalar CSR with global column ids, rows [row0, row0+n)
+__global__ void pcg_diag_kernel(long long n, long long row0, const long long* __restrict__ rowptr, const int* __restrict__ col,
+                                const double* __restrict__ val, double* __restrict__ iA) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        double d = 0.0;
+        for (long long k = rowptr[i]; k < rowptr[i + 1]; k++) if (col[k] == row0 + i) d = val[k];
+        iA[i] = 1.0 / d;
+    }
+}
+
+// x = 0, r = b, z = M^{-1} r, d = z; partials of r.r and r.z          (solver_cg.hpp:74-85)
+__global__ void pcg_init_kernel(long long n, int precond, const double* __restrict__ b, const double* __restrict__ iA,
+                                double* __restrict__ x, double* __restrict__ r, double* __restrict__ z, double* __restrict__ d,
+                                double* __restrict__ parts_rr, double* __restrict__ parts_rz) {
+    __shared__ double sh[32];
+    double rr = 0.0, rz = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        double ri = b[i], zi = precond ? iA[i] * ri : ri;
+        x[i] = 0.0; r[i] = ri; z[i] = zi; d[i] = zi;
+        rr += ri * ri; rz += ri * zi;
+    }
+    double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
+    t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
+}
+__global__ void pcg_init_state_kernel(int nparts, const double* parts_rr, const double* parts_rz, CgState* st) {
+    __shared__ double sh[32];
+    double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
+    if (threadIdx.x == 0) { st->rho = rz; st->nr0 = sqrt(rr); st->relres = 1.0; st->iters = 0; st->done = 0; st->reason = PB_CG_MAX_ITER_REACHED; }
+}
+
+// y = A d (+ partials of d.y).  LPR lanes cooperate on one row (rows have <= 7*F entries), so a warp reads
+// 32/LPR consecutive rows = one contiguous run of val/col.  xoff: d is stored for columns [xoff, ...).
+template <int LPR>
+__global__ void pcg_spmv_kernel(long long n, long long xoff, const long long* __restrict__ rowptr, const int* __restrict__ col,
+                                const double* __restrict__ val, const double* __restrict__ dvec, long long down,
+                                double* __restrict__ y, double* __restrict__ parts_dy, const CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    const int sub = threadIdx.x % LPR;
+    const long long rows_per_pass = (long long)gridDim.x * blockDim.x / LPR;
+    double dy = 0.0;
+    for (long long row = (blockIdx.x * (long long)blockDim.x + threadIdx.x) / LPR; row < ((n + rows_per_pass - 1) / rows_per_pass) * rows_per_pass; row += rows_per_pass) {
+        double acc = 0.0;
+        if (row < n) {
+            long long k0 = rowptr[row], k1 = rowptr[row + 1];
+            for (long long k = k0 + sub; k < k1; k += LPR) acc += val[k] * dvec[col[k] - xoff];
+        }
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, LPR);
+        if (sub == 0 && row < n) { y[row] = acc; dy += acc * dvec[down + row]; }
+    }
+    double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
+}
+
+// alpha = rho / (d.y); x += alpha d; r -= alpha y; z = M^{-1} r; partials of r.r, r.z   (solver_cg.hpp:106-110, 127)
+__global__ void pcg_xrz_kernel(long long n, int precond, int nparts, const double* __restrict__ parts_dy, const double* __restrict__ iA,
+                               const double* __restrict__ d, const double* __restrict__ y, double* __restrict__ x, double* __restrict__ r,
+                               double* __restrict__ z, double* __restrict__ parts_rr, double* __restrict__ parts_rz, const CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    double dy = reduce_partials(parts_dy, nparts, sh);
+    double alpha = st->rho / dy;
+    double rr = 0.0, rz = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        double di = d[i];
+        x[i] = x[i] + alpha * di;
+        double ri = r[i] - alpha * y[i];
+        double zi = precond ? iA[i] * ri : ri;
+        r[i] = ri; z[i] = zi;
+        rr += ri * ri; rz += ri * zi;
+    }
+    double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
+    t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
+}
+
+// exit tests in the reference's order (solver_cg.hpp:112-125), then beta = (r.z)/rho, d = z + beta d, iter++.
+// `iter` = number of completed direction updates before this call.
+__global__ void pcg_dir_kernel(long long n, int nparts, const double* __restrict__ parts_rr, const double* __restrict__ parts_rz,
+                               const double* __restrict__ z, double* __restrict__ d, long long iter, double tol, double divtol,
+                               long long max_iter, CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
+    double rel = sqrt(rr) / st->nr0;
+    int reason = -1;
+    if (rel < tol) reason = PB_CG_CONVERGED;
+    else if (iter > max_iter) reason = PB_CG_MAX_ITER_REACHED;
+    else if (rel > divtol) reason = PB_CG_DIVERGED;
+    double rho = st->rho;
+    // all blocks must have read st before block 0 may overwrite it: the update is deferred to pcg_commit_kernel
+    if (reason >= 0) return;
+    double beta = rz / rho;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        d[i] = z[i] + beta * d[i];
+}
+// single-block bookkeeping after pcg_dir_kernel: same decisions, written once
+__global__ void pcg_commit_kernel(int nparts, const double* parts_rr, const double* parts_rz, long long iter, double tol, double divtol,
+                                  long long max_iter, CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
+    if (threadIdx.x != 0) return;
+    double rel = sqrt(rr) / st->nr0;
+    int reason = -1;
+    if (rel < tol) reason = PB_CG_CONVERGED;
+    else if (iter > max_iter) reason = PB_CG_MAX_ITER_REACHED;
+    else if (rel > divtol) reason = PB_CG_DIVERGED;
+    st->relres = rel;
+    if (reason >= 0) { st->done = 1; st->reason = reason; st->iters = iter; }
+    else { st->rho = rz; st->iters = iter + 1; }
+}
+
+}  // namespace pb

@@ -1,0 +1,130 @@
+// K3 — structure of the condensed face system and the scatter of the per-cell condensed blocks into it.
+// Replaces assembler::assemble / finalize (hho.hpp:344-406, 451-455): instead of pushing n_loc^2 triplets per cell
+// and sorting them, the CSR pattern (union of the dense local blocks, explicit zeros kept — SURVEY App. A.9) is
+// derived from the closed-form numbering and every CSR entry GATHERS its <= 2 contributions through a precomputed
+// insertion map, so the result is deterministic and stores are coalesced.
+#pragma once
+#include "pb_device.cuh"
+
+namespace pb {
+
+// which rows this context owns: compressed face ids [cf_begin, cf_end); local cells = rows [cell_row0, row_end)
+struct Strip {
+    long long cf_begin, cf_end;      // owned block rows
+    long long cell_row0;             // first local cell row (row_begin - 1 when a ghost row below exists)
+    long long col_lo, col_hi;        // compressed face ids referenced by owned rows: [col_lo, col_hi)
+};
+
+// compressed face id -> (horizontal?, i, j)   (inverse of compress_h / compress_v)
+PB_HD void decompress_face(const Grid& g, long long cf, bool& horiz, long long& i, long long& j) {
+    if (cf < g.Nx - 1) { horiz = false; i = cf + 1; j = 0; return; }
+    long long t = cf - (g.Nx - 1), per = 2 * g.Nx - 1;
+    j = 1 + t / per; long long l = t % per;
+    if (l == 0) { horiz = true; i = 0; }
+    else if (l & 1) { horiz = true; i = (l + 1) / 2; }
+    else { horiz = false; i = l / 2; }
+}
+// first compressed id of face-row j (faces with ids j*(2Nx+1)...)
+PB_HD long long compress_row_start(const Grid& g, long long j) { return j == 0 ? 0 : (g.Nx - 1) + (j - 1) * (2 * g.Nx - 1); }
+
+struct BlockRow {            // one per owned block row (free face)
+    int cell[2];             // local cell index of the two cells sharing the face (always two: free faces are interior)
+    unsigned char li[2];     // local face index of this face inside each cell
+    unsigned char nb;        // number of column blocks
+    unsigned char pad;
+    int bcol[7];             // compressed face ids of the column blocks, ascending
+    unsigned char src[2][7]; // local face index inside cell k that feeds column block b, 255 = none
+};
+
+__global__ void build_block_rows_kernel(Grid g, Strip st, BlockRow* rows, int* nb_out) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    long long nrows = st.cf_end - st.cf_begin;
+    if (t >= nrows) return;
+    long long cf = st.cf_begin + t;
+    bool horiz; long long i, j; decompress_face(g, cf, horiz, i, j);
+    long long ci[2], cj[2]; int li[2];
+    if (horiz) { ci[0] = i; cj[0] = j - 1; li[0] = 2; ci[1] = i; cj[1] = j; li[1] = 0; }
+    else       { ci[0] = i - 1; cj[0] = j; li[0] = 1; ci[1] = i; cj[1] = j; li[1] = 3; }
+    BlockRow br;
+    long long ids[8]; unsigned char s0[8], s1[8]; int n = 0;
+    for (int k = 0; k < 2; k++) {
+        br.cell[k] = (int)((cj[k] - st.cell_row0) * g.Nx + ci[k]);
+        br.li[k] = (unsigned char)li[k];
+        for (int lf = 0; lf < 4; lf++) {
+            if (cell_face_dirichlet(g, ci[k], cj[k], lf)) continue;
+            long long id = cell_face_compressed(g, ci[k], cj[k], lf);
+            int pos = -1;
+            for (int m = 0; m < n; m++) if (ids[m] == id) pos = m;
+            if (pos < 0) { pos = n++; ids[pos] = id; s0[pos] = 255; s1[pos] = 255; }
+            if (k == 0) s0[pos] = (unsigned char)lf; else s1[pos] = (unsigned char)lf;
+        }
+    }
+    // insertion sort by compressed id (n <= 7)
+    for (int a = 1; a < n; a++) {
+        long long id = ids[a]; unsigned char x0 = s0[a], x1 = s1[a]; int b = a - 1;
+        while (b >= 0 && ids[b] > id) { ids[b + 1] = ids[b]; s0[b + 1] = s0[b]; s1[b + 1] = s1[b]; b--; }
+        ids[b + 1] = id; s0[b + 1] = x0; s1[b + 1] = x1;
+    }
+    br.nb = (unsigned char)n; br.pad = 0;
+    for (int m = 0; m < 7; m++) { br.bcol[m] = m < n ? (int)ids[m] : -1; br.src[0][m] = m < n ? s0[m] : 255; br.src[1][m] = m < n ? s1[m] : 255; }
+    rows[t] = br; nb_out[t] = n;
+}
+
+// rowptr / col of the scalar CSR from the block structure.  brp = exclusive scan of nb.
+__global__ void fill_csr_pattern_kernel(long long nrows_blk, int F, const BlockRow* rows, const long long* brp,
+                                        long long* rowptr, int* col) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;   // one thread per scalar row
+    if (t > nrows_blk * F) return;
+    if (t == nrows_blk * F) { rowptr[t] = brp[nrows_blk] * F * F; return; }
+    long long br = t / F; int a = (int)(t - br * F);
+    const BlockRow& R = rows[br];
+    long long base = brp[br] * F * F + (long long)a * R.nb * F;
+    rowptr[t] = base;
+    for (int b = 0; b < R.nb; b++)
+        for (int bc = 0; bc < F; bc++) col[base + b * F + bc] = R.bcol[b] * F + bc;
+}
+
+// values: one thread per scalar entry, grouped so that consecutive threads write consecutive CSR entries.
+// S is [cell][NF*NF] column-major (symmetric); entry (row li*F+a, col lj*F+bc).
+__global__ void scatter_values_kernel(long long nrows_blk, int F, const BlockRow* rows, const long long* brp,
+                                      const double* __restrict__ S, double* __restrict__ val) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;   // scalar row
+    // thread layout: blockDim.x = 32 * k; each warp handles consecutive entries of consecutive rows
+    long long total_rows = nrows_blk * F;
+    // one warp per 32 consecutive entries would need a search; instead loop: each thread owns a scalar row and the
+    // warp cooperatively walks the rows of its 32-row window so that stores are contiguous.
+    int lane = threadIdx.x & 31;
+    long long row0 = t - lane;
+    const int NF = 4 * F;
+    for (int rr = 0; rr < 32; rr++) {
+        long long row = row0 + rr;
+        if (row >= total_rows) break;
+        long long br = row / F; int a = (int)(row - br * F);
+        const BlockRow& R = rows[br];
+        long long base = brp[br] * F * F + (long long)a * R.nb * F;
+        int len = R.nb * F;
+        for (int e = lane; e < len; e += 32) {
+            int b = e / F, bc = e - b * F;
+            double v = 0.0;
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+                unsigned char lj = R.src[k][b];
+                // S is symmetric up to rounding: read the transposed entry so that bc runs over contiguous doubles
+                if (lj != 255) v += S[(long long)R.cell[k] * (NF * NF) + (R.li[k] * F + a) * NF + lj * F + bc];
+            }
+            val[base + e] = v;
+        }
+    }
+}
+
+// rhs: one thread per scalar row; g is [cell][NF] (already Dirichlet-lifted)
+__global__ void scatter_rhs_kernel(long long nrows_blk, int F, const BlockRow* rows, const double* __restrict__ g, double* __restrict__ rhs) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= nrows_blk * F) return;
+    long long br = t / F; int a = (int)(t - br * F);
+    const BlockRow& R = rows[br];
+    const int NF = 4 * F;
+    rhs[t] = g[(long long)R.cell[0] * NF + R.li[0] * F + a] + g[(long long)R.cell[1] * NF + R.li[1] * F + a];
+}
+
+}  // namespace pb

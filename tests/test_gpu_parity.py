@@ -1,0 +1,157 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against the CPU oracle.
+Bars (BASELINE.json north_star): local matrices 1e-11 relative (Frobenius), numbering and sparsity pattern
+bit-exact, discrete solution 1e-8 relative."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+pytestmark = pytest.mark.gpu
+
+import proton_b200 as pb
+from proton_b200 import PB
+from oracle import orc
+
+TOL_LOCAL = 1e-11
+TOL_SOL = 1e-8
+
+
+def frob_rel(a, b):
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pb.Context(0)
+    yield c
+    c.close()
+
+
+def oracle_locals(m, cd, fd, stab, problem=0, fun=0, rhs_di=0):
+    out = [m.local(c, cd, fd, stab=stab, problem=problem, fun=fun, rhs_di=rhs_di) for c in range(m.ncells)]
+    return out
+
+
+def schur_of(S):
+    """Condensed face system of the oracle's full system: K_FF - K_FT K_TT^-1 K_TF and the matching rhs."""
+    K = S.matrix().tocsc()
+    nT = S.cbs * S.mesh.ncells
+    KTT, KTF, KFT, KFF = K[:nT, :nT], K[:nT, nT:], K[nT:, :nT], K[nT:, nT:]
+    lu = spla.splu(KTT)
+    X = lu.solve(KTF.toarray())
+    Sc = KFF.toarray() - KFT @ X
+    g = S.rhs[nT:] - KFT @ lu.solve(S.rhs[:nT])
+    return Sc, g, KFF.tocsr()
+
+
+@pytest.mark.parametrize("k", [0, 1, 2, 3])
+@pytest.mark.parametrize("stab", [PB.STAB_FANCY, PB.STAB_NAIVE])
+def test_local_operators_tensor(ctx, k, stab):
+    N = 6
+    m = orc.Mesh(N)
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx.mesh(pb.mesh_init_params(N, N)).assemble(hdi, stab_kind=stab, keep_local=True)
+    lc = ctx.local(PB.LOCAL_LC); oper = ctx.local(PB.LOCAL_OPER); rhs = ctx.local(PB.LOCAL_RHS)
+    ref = oracle_locals(m, k + 1, k, stab)
+    worst = 0.0
+    for c in range(m.ncells):
+        r = ref[c]
+        worst = max(worst, frob_rel(lc[c], r["data"] + r["stab"]), frob_rel(oper[c][: hdi.rbs - 1], r["oper"]), frob_rel(rhs[c], r["rhs"]))
+    assert worst < TOL_LOCAL, worst
+
+
+def test_numbering_bit_exact(ctx):
+    Nx, Ny = 7, 5
+    m = orc.Mesh(Nx, Ny)
+    ctx.mesh(pb.mesh_init_params(Nx, Ny))
+    assert np.array_equal(ctx.cell_faces(), m.cells()[1])
+    S = m.assemble(1, 0)
+    _, dirichlet = m.faces()
+    ct = ctx.compress_table()
+    assert np.array_equal(ct[dirichlet == 0], S.compress[dirichlet == 0])
+    assert np.all(ct[dirichlet == 1] == -1)
+    assert np.array_equal(ctx.points(), m.points())
+
+
+@pytest.mark.parametrize("k,N", [(0, 8), (1, 8), (2, 8), (3, 6), (1, (9, 5))])
+def test_condensed_system_pattern_and_values(ctx, k, N):
+    Nx, Ny = N if isinstance(N, tuple) else (N, N)
+    m = orc.Mesh(Nx, Ny)
+    S = m.assemble(k + 1, k)
+    Sc, g, KFF = schur_of(S)
+    ctx.mesh(pb.mesh_init_params(Nx, Ny)).assemble(pb.hho_degree_info(k + 1, k))
+    rp, col, val, rhs = ctx.csr()
+    # pattern == face-face block of the reference LHS pattern, bit-exact (explicit zeros included)
+    KFF.sort_indices()
+    assert np.array_equal(rp, KFF.indptr.astype(np.int64))
+    assert np.array_equal(col, KFF.indices.astype(np.int32))
+    A = sp.csr_matrix((val, col, rp), shape=Sc.shape).toarray()
+    assert frob_rel(A, Sc) < TOL_LOCAL
+    assert frob_rel(rhs, g) < 1e-10
+
+
+@pytest.mark.parametrize("k,N", [(0, 16), (1, 16), (2, 16), (3, 8)])
+def test_pcg_solution_matches_full_system_direct_solve(ctx, k, N):
+    m = orc.Mesh(N)
+    S = m.assemble(k + 1, k)
+    sol = spla.splu(S.matrix().tocsc()).solve(S.rhs)
+    ctx.mesh(pb.mesh_init_params(N, N)).assemble(pb.hho_degree_info(k + 1, k))
+    res = ctx.conjugated_gradient(pb.cg_params(convergence_threshold=1e-13, max_iter=3 * ctx.n_rows, apply_preconditioner=True))
+    assert res["exit_reason"] == PB.CG_CONVERGED
+    full = ctx.recover()
+    nT = S.cbs * m.ncells
+    assert frob_rel(full[nT:], sol[nT:]) < TOL_SOL
+    assert frob_rel(full[:nT], sol[:nT]) < TOL_SOL
+    # error norms of convergence_test.cpp:254-306 evaluated by the oracle on the GPU solution
+    e_gpu = np.sqrt(np.array(S.errors_convergence(full))); e_ref = np.sqrt(np.array(S.errors_convergence(sol)))
+    assert np.max(np.abs(e_gpu - e_ref) / e_ref) < TOL_SOL
+
+
+def test_pcg_iteration_count_matches_reference_cg(ctx):
+    """Same algorithm => same iteration count and residual history end as solver_cg.hpp on the same matrix."""
+    N, k = 16, 1
+    ctx.mesh(pb.mesh_init_params(N, N)).assemble(pb.hho_degree_info(k + 1, k))
+    rp, col, val, rhs = ctx.csr()
+    for precond in (True, False):
+        x_ref, e_ref, it_ref, rr_ref, _ = orc.cg(rp, col, val, rhs, tol=1e-12, max_iter=3 * len(rhs), precond=precond)
+        res = ctx.conjugated_gradient(pb.cg_params(convergence_threshold=1e-12, max_iter=3 * len(rhs), apply_preconditioner=precond))
+        assert res["exit_reason"] == e_ref
+        assert abs(res["iterations"] - it_ref) <= 1
+        assert frob_rel(ctx.face_solution(), x_ref) < 1e-9
+
+
+@pytest.mark.parametrize("k", [0, 1, 2])
+def test_local_operators_poly_dunavant(ctx, k):
+    """uncut cells of the cut driver: Dunavant fan quadrature + naive stabilisation."""
+    N = 5
+    m = orc.Mesh(N, poly=True)
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT).assemble(hdi, stab_kind=PB.STAB_NAIVE, keep_local=True)
+    lc = ctx.local(PB.LOCAL_LC); rhs = ctx.local(PB.LOCAL_RHS)
+    worst = 0.0
+    for c in range(m.ncells):
+        r = m.local(c, k + 1, k, stab=orc.STAB_NAIVE)
+        worst = max(worst, frob_rel(lc[c], r["data"] + r["stab"]), frob_rel(rhs[c], r["rhs"]))
+    assert worst < TOL_LOCAL, worst
+
+
+def test_distorted_quads(ctx):
+    """general (non-rectangular) quads: displaced interior nodes, as move_nodes produces near the interface."""
+    N, k = 6, 2
+    m = orc.Mesh(N)
+    ctx.mesh(pb.mesh_init_params(N, N))
+    xy = ctx.points()
+    rng = np.random.default_rng(0)
+    interior = np.ones(len(xy), bool)
+    interior[(xy[:, 0] < 1e-12) | (xy[:, 0] > 1 - 1e-12) | (xy[:, 1] < 1e-12) | (xy[:, 1] > 1 - 1e-12)] = False
+    xy[interior] += rng.uniform(-0.2 / N, 0.2 / N, size=(interior.sum(), 2))
+    ctx.set_points(xy)
+    import ctypes as C
+    from oracle.orc import lib as olib
+    # push the same points into the oracle mesh
+    olib().orc_mesh_set_points(m.h, xy.ctypes.data_as(C.POINTER(C.c_double)))
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx.assemble(hdi, keep_local=True)
+    lc = ctx.local(PB.LOCAL_LC)
+    worst = max(frob_rel(lc[c], (lambda r: r["data"] + r["stab"])(m.local(c, k + 1, k))) for c in range(m.ncells))
+    assert worst < TOL_LOCAL, worst
