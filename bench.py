@@ -1,0 +1,242 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the HHO hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--N 2048] [--k 2]
+
+One step = stages 1+2 of the hot path over one batch: per-cell local operators + static condensation (K1) and the
+scatter into the condensed CSR system + rhs (K3) on a synthetic uniform-quad mesh (workload: BASELINE config 3,
+uncut HHO Poisson k=2 on 2048x2048 quads per GPU; N>1 stacks N such strips: weak scaling, no data-path collective).
+`value` = cells assembled+condensed per second (whole job).  Stage 3 (PCG on the condensed system) is timed after
+the K steps and reported under "cg" with its own HBM roofline.  `e2e` = the same metric through the C ABI with
+host buffers: pinned host points -> device, assemble, condensed rhs -> pinned host, every step.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# reference-algorithm flop count per uncut cell, HHO(k+1,k), fancy stabilisation, with condensation
+FLOP_PER_CELL = {0: 2.4e3, 1: 18.2e3, 2: 72.7e3, 3: 213e3}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.rows, self.index, self.p = [], index, None
+
+    def __enter__(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.p = None
+        return self
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.p:
+            time.sleep(0.15); self.p.terminate()
+            try: self.p.wait(timeout=2)
+            except Exception: self.p.kill()
+
+    def summary(self):
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """The reference's own CPU path for stages 1+2 (per-cell operators + assembler.assemble + finalize), timed on the
+    host cores.  The reference cannot be built here or on the box (Eigen3/SILO/Lua absent), so this is the plain-C++
+    restatement in oracle/ (kind "port"), single-threaded like the reference, on a bounded sample of the workload."""
+    if rank != 0:
+        return
+    from oracle import orc
+    k, Ns = args.k, args.ref_N
+    m = orc.Mesh(Ns)
+    vals = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        S = m.assemble(k + 1, k)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            vals.append(dt)
+        last = S
+    ms = 1e3 * sum(vals) / len(vals)
+    v = m.ncells / (ms * 1e-3)
+    # reference CG (solver_cg.hpp) on its own full system: time per iteration
+    x, e, it, rr, sec = orc.cg(last.rowptr, last.col, last.val, last.rhs, tol=1e-12, max_iter=3 * last.n, precond=True)
+    sample = f"uncut HHO({k+1},{k}) on {Ns}x{Ns} quads (cells/s is size-independent; the full {args.N}^2 exceeds the reference's 32-bit sparse indices)"
+    out = {"metric": "HHO cells assembled+condensed/sec", "value": v, "unit": "cells/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "impl": "reference", "config": {"workload": f"uncut HHO Poisson k={k} on {args.N}x{args.N} quads per GPU (BASELINE config 3)", "sample": sample},
+           "cpu_baseline": {"value": v, "unit": "cells/s", "cores": 1, "kind": "port", "sample": sample,
+                            "stage_seconds": {"local_operators": last.seconds_local, "assemble_finalize": last.seconds_global}},
+           "cg": {"unknowns": last.n, "iterations": it, "solve_ms": sec * 1e3, "ms_per_iter": sec * 1e3 / max(it + 1, 1), "system": "full cell+face system (the reference has no condensation)"},
+           "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import proton_b200 as pb
+    from proton_b200 import PB
+    L = pb.lib()
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = local_rank
+    k, N = args.k, args.N
+    Nx, Ny = N, N * world                      # weak scaling: every rank owns an N x N strip of an N x (N*world) mesh
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx = pb.Context(dev)
+    ctx.mesh(pb.mesh_init_params(Nx, Ny, 0.0, 1.0, 0.0, float(world)), PB.QUAD_TENSOR_GAUSS, row_begin=rank * N, row_end=(rank + 1) * N)
+    fp64_peak = ctx.probe_fp64_peak()
+    cells_rank = N * N                         # owned cells (the ghost row assembled for the strip's bottom faces is not counted)
+
+    def sync_all():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---------------- value: inputs resident in HBM
+    for _ in range(args.warmup):
+        ctx.assemble(hdi)
+    sync_all()
+    dev_ms, k1_ms = [], []
+    with ClockSampler(dev) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ctx.assemble(hdi)
+            t = ctx.timings(); dev_ms.append(t["ms_local"] + t["ms_scatter"]); k1_ms.append(t["ms_local"])
+        sync_all()
+        wall_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    ms_step = sum(dev_ms) / len(dev_ms)
+    k1 = sum(k1_ms) / len(k1_ms)
+    n_rows, nnz = ctx.n_rows, ctx.nnz
+
+    # ---------------- e2e: host buffers through the C ABI, copies inside the timed region
+    pts_host = torch.empty((ctx.npoints, 2), dtype=torch.float64).pin_memory()
+    L.pb_mesh_get_points(ctx._h, C.c_void_p(pts_host.data_ptr()))
+    rhs_host = torch.empty(n_rows, dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        assert L.pb_mesh_set_points(ctx._h, C.c_void_p(pts_host.data_ptr())) == 0
+        ctx.assemble(hdi)
+        assert L.pb_get_csr(ctx._h, None, None, None, C.c_void_p(rhs_host.data_ptr())) == 0
+    for _ in range(max(1, args.warmup // 2)):
+        e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    sync_all()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    checksum = float(rhs_host.sum())
+
+    # ---------------- stage 3: PCG on the condensed system (single-rank contexts; see DESIGN.md for the multi-rank plan)
+    cg = None
+    if world == 1:
+        hbm, hbm_src = peaks()
+        spmv_bytes = 12.0 * nnz + 20.0 * n_rows
+        iter_bytes = spmv_bytes + 11 * 8.0 * n_rows                 # + vector passes of the dir / xrz kernels
+        ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))          # warm-up + the reference's own problem
+        r_tol = ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))
+        t_tol = ctx.timings()["ms_pcg"]
+        fixed = 200
+        r_fix = ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, fixed, True))            # fixed-iteration run for bandwidth
+        t_fix = ctx.timings()["ms_pcg"]
+        its = r_fix["iterations"] + 1
+        ms_it = t_fix / its
+        cg = {"unknowns": n_rows, "nnz": nnz, "tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": t_tol,
+              "fixed_iterations": its, "ms_per_iter": ms_it, "iter_bytes": iter_bytes,
+              "roofline": {"bound": "hbm", "achieved": iter_bytes / (ms_it * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                           "frac": iter_bytes / (ms_it * 1e-3) / 1e9 / hbm, "peak_source": hbm_src, "traffic": None}}
+
+    # ---------------- reduce over ranks (max time), print on rank 0
+    if dist is not None:
+        tt = torch.tensor([ms_step, k1, e2e_ms, wall_ms], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step, k1, e2e_ms, wall_ms = [float(v) for v in tt.tolist()]
+    cells_total = cells_rank * world
+    value = cells_total / (ms_step * 1e-3)
+    flop = FLOP_PER_CELL[k]
+    k1_cells = ctx.ncells_local                                      # K1 also computes the ghost row
+    achieved_tf = k1_cells * flop / (k1 * 1e-3) / 1e12
+    out = {"metric": "HHO cells assembled+condensed/sec", "value": value, "unit": "cells/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms_step, "wall_ms_per_step": wall_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"uncut HHO Poisson k={k} on {N}x{N} quads per GPU (BASELINE config 3), HHO({k+1},{k}), tensor Gauss, fancy stabilisation, "
+                                  f"f=2pi^2 sin(pi x)sin(pi y)", "mesh": [Nx, Ny], "l2": "working set >> L2 (per-step outputs %.1f GB)" % ((ctx.ncells_local * (16 * hdi.fbs * hdi.fbs + 4 * hdi.fbs) * 8 + nnz * 8) / 1e9),
+                      "partition": f"{world} strips of cell rows, one ghost row each, no collective in stages 1+2"},
+           "clocks": clk.summary(),
+           "roofline": {"bound": "fp64", "kernel": "local_uncut_kernel (K1)", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp64_peak,
+                        "peak_source": "measured on this GPU by pb_probe_fp64_peak (register-resident DFMA chains); MEASURED_PEAKS.json has no fp64 entry",
+                        "flop_per_cell": flop, "flop_model": "reference-algorithm flops (SURVEY 8d), not executed flops", "ms_per_launch": k1, "traffic": None},
+           "e2e": {"value": cells_total / (e2e_ms * 1e-3), "unit": "cells/s", "h2d_bytes_per_step": int(ctx.npoints * 16), "d2h_bytes_per_step": int(n_rows * 8),
+                   "ms_per_step": e2e_ms, "rhs_checksum": checksum},
+           "gpu_launches": 3 * args.steps, "cg": cg}
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import orc
+            m = orc.Mesh(args.cpu_N)
+            t0 = time.perf_counter(); S = m.assemble(k + 1, k); dt = time.perf_counter() - t0
+            out["cpu_baseline"] = {"value": m.ncells / dt, "unit": "cells/s", "cores": 1, "kind": "port",
+                                   "sample": f"same workload on {args.cpu_N}x{args.cpu_N} cells, oracle/ restatement of the reference's serial assembly loop (-O3 -mavx), {dt:.1f} s"}
+        print(json.dumps(out), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--N", type=int, default=2048)
+    ap.add_argument("--k", type=int, default=2)
+    ap.add_argument("--ref-N", dest="ref_N", type=int, default=128)
+    ap.add_argument("--cpu-N", dest="cpu_N", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -307,7 +307,7 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->cell_loc != nullptr, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_upload first");
     int sk = p->stab_kind == PB_STAB_FANCY ? 1 : 0;
     const int rqd = 2 * (cd + p->rhs_degree_increase);
-    bool relayout = !ctx->assembled || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc);
+    bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc);
     ctx->prm = *p; ctx->CD = cd; ctx->FD = fd;
     ctx->C = cell_basis_size(cd); ctx->F = fd + 1; ctx->R = cell_basis_size(fd + 1); ctx->NF = 4 * ctx->F; ctx->N = ctx->C + ctx->NF;
     const long long nc = ctx->ncells_local;
