@@ -75,6 +75,7 @@ static void fill_quad_tables(QuadTables& t) {
       double a1 = 5.0, a2 = 2.0 * std::sqrt(10.0 / 7.0);
       double q = std::sqrt(a1 - a2) / 3.0, w = (322 + 13.0 * std::sqrt(70.0)) / 900.0; t.gx[5][1] = -q; t.gx[5][2] = q; t.gw[5][1] = t.gw[5][2] = w;
       q = std::sqrt(a1 + a2) / 3.0; w = (322 - 13.0 * std::sqrt(70.0)) / 900.0; t.gx[5][3] = -q; t.gx[5][4] = q; t.gw[5][3] = t.gw[5][4] = w; }
+    for (int a = 0; a < 45; a++) { t.mono_x[a] = mono_px(a); t.mono_y[a] = mono_py(a); }
     struct Orb { int rule, kind; double a, b, c, w; };
     static const Orb orbs[] = {
         {0, 1, 0.333333333333333, 0, 0, 1.000000000000000},
@@ -230,12 +231,12 @@ extern "C" pb_status pb_cut_preprocess_circle(pb_ctx* ctx, double, double, doubl
 }
 
 // ------------------------------------------------------------------------------------------------ stage 1+2
-template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB>
+template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB>
 static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A) {
     constexpr int QC = cell_qps(QK, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
     using SM = LocalSmem<CD, FD, QCMAX>;
     const size_t smem = sizeof(SM) * (TPB / GS);
-    auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS>;
+    auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS, TPB, MINB>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int bps = 0, nsm = 0;
@@ -251,17 +252,21 @@ static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A) {
 // (cell degree, face degree, quadrature kind, stabilisation, load quadrature degree) -> kernel instance
 static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd, int qk, int sk, int rqd, bool* found) {
     *found = true;
-#define PB_CASE(CD_, FD_, QK_, SK_, RQD_, GS_, TPB_) \
-    if (cd == CD_ && fd == FD_ && qk == QK_ && sk == SK_ && rqd == RQD_) return launch_local<CD_, FD_, QK_, SK_, RQD_, GS_, TPB_>(c, A);
+#define PB_CASE(CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_) \
+    if (cd == CD_ && fd == FD_ && qk == QK_ && sk == SK_ && rqd == RQD_) return launch_local<CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_>(c, A);
+#ifdef PB_FAST_BUILD   // developer builds: only the headline instance
+    PB_CASE(3, 2, 0, 1, 6, 32, 128, 4)
+#else
     // HHO(k+1,k), tensor Gauss (convergence_test): fancy and naive
-    PB_CASE(1, 0, 0, 1, 2, 8, 256)  PB_CASE(1, 0, 0, 0, 2, 8, 256)
-    PB_CASE(2, 1, 0, 1, 4, 16, 256) PB_CASE(2, 1, 0, 0, 4, 16, 256)
-    PB_CASE(3, 2, 0, 1, 6, 32, 256) PB_CASE(3, 2, 0, 0, 6, 32, 256)
-    PB_CASE(4, 3, 0, 1, 8, 32, 128) PB_CASE(4, 3, 0, 0, 8, 32, 128)
+    PB_CASE(1, 0, 0, 1, 2, 8, 256, 4)  PB_CASE(1, 0, 0, 0, 2, 8, 256, 4)
+    PB_CASE(2, 1, 0, 1, 4, 16, 128, 6) PB_CASE(2, 1, 0, 0, 4, 16, 128, 6)
+    PB_CASE(3, 2, 0, 1, 6, 32, 128, 4) PB_CASE(3, 2, 0, 0, 6, 32, 128, 4)
+    PB_CASE(4, 3, 0, 1, 8, 32, 128, 2) PB_CASE(4, 3, 0, 0, 8, 32, 128, 2)
     // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive
-    PB_CASE(1, 0, 1, 0, 2, 8, 256)
-    PB_CASE(2, 1, 1, 0, 4, 16, 256)
-    PB_CASE(3, 2, 1, 0, 6, 32, 256)
+    PB_CASE(1, 0, 1, 0, 2, 8, 256, 4)
+    PB_CASE(2, 1, 1, 0, 4, 16, 128, 6)
+    PB_CASE(3, 2, 1, 0, 6, 32, 128, 4)
+#endif
 #undef PB_CASE
     *found = false; return cudaSuccess;
 }

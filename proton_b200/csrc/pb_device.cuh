@@ -38,6 +38,8 @@ struct QuadTables {
     // Dunavant rules 1..8 as rows {l0,l1,l2,w} (quadratures_dunavant.hpp:27-118), index 8 = the empty sentinel
     double dun[9][16][4];
     int dun_n[9];
+    // graded monomial index -> exponents (bases.hpp:114-127), degrees 0..8
+    int mono_x[45], mono_y[45];
 };
 static __constant__ QuadTables c_qt;   // one translation unit (pb_api.cu) includes this header
 
