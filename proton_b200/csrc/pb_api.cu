@@ -255,17 +255,17 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
 #define PB_CASE(CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_) \
     if (cd == CD_ && fd == FD_ && qk == QK_ && sk == SK_ && rqd == RQD_) return launch_local<CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_>(c, A);
 #ifdef PB_FAST_BUILD   // developer builds: only the headline instance
-    PB_CASE(3, 2, 0, 1, 6, 32, 128, 4)
+    PB_CASE(3, 2, 0, 1, 6, 8, 32, 5)
 #else
     // HHO(k+1,k), tensor Gauss (convergence_test): fancy and naive
-    PB_CASE(1, 0, 0, 1, 2, 8, 256, 4)  PB_CASE(1, 0, 0, 0, 2, 8, 256, 4)
-    PB_CASE(2, 1, 0, 1, 4, 16, 128, 6) PB_CASE(2, 1, 0, 0, 4, 16, 128, 6)
-    PB_CASE(3, 2, 0, 1, 6, 32, 128, 4) PB_CASE(3, 2, 0, 0, 6, 32, 128, 4)
-    PB_CASE(4, 3, 0, 1, 8, 32, 128, 2) PB_CASE(4, 3, 0, 0, 8, 32, 128, 2)
+    PB_CASE(1, 0, 0, 1, 2, 8, 64, 8)  PB_CASE(1, 0, 0, 0, 2, 8, 64, 8)
+    PB_CASE(2, 1, 0, 1, 4, 8, 32, 8) PB_CASE(2, 1, 0, 0, 4, 8, 32, 8)
+    PB_CASE(3, 2, 0, 1, 6, 8, 32, 5) PB_CASE(3, 2, 0, 0, 6, 8, 32, 5)
+    PB_CASE(4, 3, 0, 1, 8, 16, 32, 5) PB_CASE(4, 3, 0, 0, 8, 16, 32, 5)
     // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive
-    PB_CASE(1, 0, 1, 0, 2, 8, 256, 4)
-    PB_CASE(2, 1, 1, 0, 4, 16, 128, 6)
-    PB_CASE(3, 2, 1, 0, 6, 32, 128, 4)
+    PB_CASE(1, 0, 1, 0, 2, 8, 64, 8)
+    PB_CASE(2, 1, 1, 0, 4, 8, 32, 8)
+    PB_CASE(3, 2, 1, 0, 6, 8, 32, 5)
 #endif
 #undef PB_CASE
     *found = false; return cudaSuccess;
