@@ -154,6 +154,20 @@ class Context:
              np.ascontiguousarray(cell_loc, np.int32), np.ascontiguousarray(iface_off, np.int64), np.ascontiguousarray(iface_pts, np.float64)]
         self._ck(lib().pb_cut_upload(self._h, *[_ptr(x) for x in a]))
 
+    def cut_levelset(self, kind=0, radius=0.35, cx=0.5, cy=0.5, cut_y=0.5):
+        self._ck(lib().pb_cut_levelset(self._h, int(kind), C.c_double(radius), C.c_double(cx), C.c_double(cy), C.c_double(cut_y)))
+
+    def cut_preprocess(self, refine_steps=4):
+        self._ck(lib().pb_cut_preprocess(self._h, int(refine_steps)))
+
+    def cut_download(self):
+        nl = np.zeros(self.npoints, np.int32); fl = np.zeros(self.nfaces, np.int32); fip = np.zeros((self.nfaces, 2))
+        cl = np.zeros(self.ncells, np.int32); ncut = C.c_longlong(); ni = C.c_int()
+        self._ck(lib().pb_cut_download(self._h, _ptr(nl), _ptr(fl), _ptr(fip), _ptr(cl), C.byref(ncut), C.byref(ni), None))
+        pts = np.zeros((ncut.value, ni.value, 2))
+        self._ck(lib().pb_cut_download(self._h, None, None, None, None, None, None, _ptr(pts)))
+        return dict(node_loc=nl, face_loc=fl, face_ip=fip, cell_loc=cl, iface_pts=pts)
+
     # ---- stages 1+2
     def assemble(self, hdi, stab_kind=PB.STAB_FANCY, problem=PB.PROBLEM_HHO, fun=PB.FUN_SINSIN, rhs_degree_increase=0, eta=5.0, keep_local=False):
         p = _AssemblyParams(hdi.cd, hdi.fd, stab_kind, problem, fun, rhs_degree_increase, eta, int(keep_local))

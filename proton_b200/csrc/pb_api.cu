@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "pb_local.cuh"
+#include "pb_cut.cuh"
 #include "pb_pcg.cuh"
 #include "pb_system.cuh"
 
@@ -27,7 +28,12 @@ struct pb_ctx {
     Grid grid{}; Strip strip{}; int quad_kind = 0;
     long long npoints = 0, ncells_local = 0, ncells_global = 0;
     double2* points = nullptr;
-    int* cell_loc = nullptr;              // local cells
+    // cutHHO user data (whole mesh)
+    LevelSet ls{}; bool have_ls = false, have_cut = false;
+    int *node_loc = nullptr, *face_loc = nullptr, *cell_loc_g = nullptr, *cut_cells = nullptr;
+    double2 *face_ip = nullptr, *iface = nullptr;
+    int ncut = 0, NI = 0;
+    long long nfaces = 0;
     // assembly
     bool assembled = false;
     pb_assembly_params prm{};
@@ -132,10 +138,15 @@ static void free_system(pb_ctx* c) {
     c->assembled = false;
 }
 
+static void free_cut(pb_ctx* c) {
+    dfree(&c->node_loc); dfree(&c->face_loc); dfree(&c->cell_loc_g); dfree(&c->cut_cells); dfree(&c->face_ip); dfree(&c->iface);
+    c->have_cut = false; c->ncut = 0; c->NI = 0;
+}
+
 extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     if (!ctx) return PB_OK;
     cudaSetDevice(ctx->device);
-    free_system(ctx); dfree(&ctx->points); dfree(&ctx->cell_loc); dfree(&ctx->cg);
+    free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->cg);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx; return PB_OK;
@@ -180,7 +191,8 @@ extern "C" pb_status pb_mesh_cartesian(pb_ctx* ctx, long long Nx, long long Ny, 
     if (s.col_hi > num_free_faces(g)) s.col_hi = num_free_faces(g);
     ctx->ncells_local = (row_end - s.cell_row0) * Nx;
     CK(dalloc(ctx, &ctx->points, (size_t)ctx->npoints));
-    dfree(&ctx->cell_loc);
+    free_cut(ctx);
+    ctx->nfaces = 2 * Nx * Ny + Nx + Ny;
     gen_points_kernel<<<148 * 4, 256, 0, ctx->stream>>>(g, ctx->points);
     CK(cudaGetLastError()); CK(cudaStreamSynchronize(ctx->stream));
     ctx->have_mesh = true; return PB_OK;
@@ -217,19 +229,7 @@ extern "C" pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table) {
     }
     return PB_OK;
 }
-extern "C" pb_status pb_cut_upload(pb_ctx* ctx, const int*, const int*, const double*, const int* cell_location, const long long*, const double*) {
-    if (!ctx) return PB_ERR_INVALID;
-    NEED(ctx->have_mesh && cell_location, PB_ERR_STATE, "pb_cut_upload: no mesh");
-    CK(cudaSetDevice(ctx->device));
-    CK(dalloc(ctx, &ctx->cell_loc, (size_t)ctx->ncells_local));
-    CK(cudaMemcpy(ctx->cell_loc, cell_location + ctx->strip.cell_row0 * ctx->grid.Nx, (size_t)ctx->ncells_local * 4, cudaMemcpyHostToDevice));
-    ctx->assembled = false;
-    return PB_OK;   // cut-cell payload is consumed by K2 (pb_local_cut.cuh) once uploaded; see DESIGN.md
-}
-extern "C" pb_status pb_cut_preprocess_circle(pb_ctx* ctx, double, double, double, int) {
-    if (!ctx) return PB_ERR_INVALID;
-    return fail(ctx, PB_ERR_UNSUPPORTED, "pb_cut_preprocess_circle: device-side preprocessing not built yet (SURVEY 8f.2)");
-}
+#include "pb_api_cut.inl"
 
 // ------------------------------------------------------------------------------------------------ stage 1+2
 template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB>
@@ -318,7 +318,7 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
         if (!(c1 || c2)) cd = fd;
     }
     NEED(p->problem == PB_PROBLEM_HHO || p->problem == PB_PROBLEM_FICTDOM, PB_ERR_INVALID, "pb_assemble: bad problem kind");
-    if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->cell_loc != nullptr, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_upload first");
+    if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");
     int sk = p->stab_kind == PB_STAB_FANCY ? 1 : 0;
     const int rqd = 2 * (cd + p->rhs_degree_increase);
     bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc);
@@ -337,7 +337,7 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     }
     LocalArgs A{};
     A.grid = ctx->grid; A.grid.row_begin = ctx->strip.cell_row0;      // local cell 0 sits in row cell_row0
-    A.points = ctx->points; A.cell_loc = p->problem == PB_PROBLEM_FICTDOM ? ctx->cell_loc : nullptr;
+    A.points = ctx->points; A.cell_loc = p->problem == PB_PROBLEM_FICTDOM ? ctx->cell_loc_g + ctx->strip.cell_row0 * ctx->grid.Nx : nullptr;
     A.ncells = nc; A.fun = p->fun; A.problem = p->problem; A.eta = p->eta;
     A.S = ctx->S; A.g = ctx->g; A.recA = ctx->recA; A.recb = ctx->recb;
     A.lc = p->keep_local ? ctx->lc : nullptr; A.oper = p->keep_local ? ctx->oper : nullptr; A.rhs = p->keep_local ? ctx->rhsloc : nullptr;
@@ -345,6 +345,9 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     bool found = false;
     CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
     if (!found) return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: no kernel instance for HHO(%d,%d) quad_kind=%d stab=%d load degree %d", cd, fd, ctx->quad_kind, p->stab_kind, rqd);
+    if (p->problem == PB_PROBLEM_FICTDOM && ctx->ncut > 0) {
+        pb_status st = launch_cut(ctx, A, cd, fd); if (st != PB_OK) return st;
+    }
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     const int F = ctx->F;
     scatter_values_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);

@@ -1,0 +1,121 @@
+"""GPU parity tests of the cutHHO (fictitious-domain) path: device-side mesh preprocessing, K2 cut-cell operators,
+condensed system and solution against the CPU oracle, and the reference's own golden energy errors
+(apps/cuthho/cuthho.xlsx, F.D. table) through the whole GPU path."""
+import numpy as np
+import pytest
+import scipy.sparse.linalg as spla
+
+pytestmark = pytest.mark.gpu
+
+import proton_b200 as pb
+from proton_b200 import PB
+from oracle import orc
+
+TOL_LOCAL = 1e-11
+TOL_SOL = 1e-8
+
+
+def frob_rel(a, b):
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pb.Context(0)
+    yield c
+    c.close()
+
+
+def gpu_cut_mesh(ctx, N, r=4, radius=0.35):
+    ctx.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT)
+    ctx.cut_levelset(0, radius, 0.5, 0.5)
+    ctx.cut_preprocess(r)
+
+
+@pytest.mark.parametrize("N,r", [(10, 4), (20, 4), (32, 4), (17, 3), (40, 5)])
+def test_cut_preprocessing_matches_oracle(ctx, N, r):
+    """detect_* / move_nodes / refine_interface on the device == the host restatement (cuthho_geom.hpp)."""
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=r)
+    ci = m.cut_info()
+    gpu_cut_mesh(ctx, N, r)
+    d = ctx.cut_download()
+    assert np.array_equal(d["node_loc"], ci["node_loc"])
+    assert np.array_equal(d["face_loc"], ci["face_loc"])
+    assert np.array_equal(d["cell_loc"], ci["cell_loc"])
+    cutf = ci["face_loc"] == orc.CUT
+    assert np.array_equal(d["face_ip"][cutf], ci["face_ip"][cutf])          # same bisection path, bit for bit
+    assert np.array_equal(ctx.points(), m.points())                       # displaced nodes
+    assert np.array_equal(d["iface_pts"].reshape(-1, 2), ci["iface_pts"])
+
+
+@pytest.mark.parametrize("k,N", [(0, 10), (1, 10), (2, 10), (1, 16)])
+def test_cut_local_operators(ctx, k, N):
+    """every cell of the fictitious-domain problem: cut cells (K2) and Dunavant-fan uncut cells (K1)."""
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=4)
+    ci = m.cut_info()
+    gpu_cut_mesh(ctx, N, 4)
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM, keep_local=True)
+    lc = ctx.local(PB.LOCAL_LC); oper = ctx.local(PB.LOCAL_OPER); rhs = ctx.local(PB.LOCAL_RHS)
+    worst_cut = worst_uncut = 0.0
+    for c in range(m.ncells):
+        r = m.local(c, k + 1, k, stab=orc.STAB_CUT, problem=1)
+        e = max(frob_rel(lc[c], r["data"] + r["stab"]), frob_rel(oper[c][: r["oper"].shape[0]], r["oper"]),
+                np.linalg.norm(rhs[c] - r["rhs"]) / max(np.linalg.norm(r["rhs"]), 1.0))
+        if ci["cell_loc"][c] == orc.CUT:
+            worst_cut = max(worst_cut, e)
+        else:
+            worst_uncut = max(worst_uncut, e)
+    assert worst_uncut < TOL_LOCAL, worst_uncut
+    assert worst_cut < 1e-10, worst_cut          # cut cells with small sub-areas have worse-conditioned gr_lhs
+
+
+@pytest.mark.parametrize("k,N", [(0, 10), (1, 10), (2, 10), (1, 20)])
+def test_fictdom_solution_and_golden_error(ctx, golden, k, N):
+    """condensed GPU solve == direct solve of the oracle's full system; energy error == the reference's table."""
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=4)
+    S = m.assemble(k + 1, k, stab=orc.STAB_CUT, problem=1)
+    sol = spla.splu(S.matrix().tocsc()).solve(S.rhs)
+    gpu_cut_mesh(ctx, N, 4)
+    ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+    res = ctx.conjugated_gradient(pb.cg_params(convergence_threshold=1e-14, max_iter=20 * ctx.n_rows, apply_preconditioner=True))
+    assert res["exit_reason"] == PB.CG_CONVERGED
+    full = ctx.recover()
+    nT = S.cbs * m.ncells
+    assert frob_rel(full[nT:], sol[nT:]) < TOL_SOL
+    assert frob_rel(full[:nT], sol[:nT]) < TOL_SOL
+    e_gpu = S.error_fictdom(full); e_ref = S.error_fictdom(sol)
+    assert abs(e_gpu - e_ref) / e_ref < TOL_SOL
+    key = f"k{k}_N{N}_r4"
+    if key in golden["cuthho_fictdom"]:
+        ref = golden["cuthho_fictdom"][key]
+        assert abs(e_gpu - ref) / ref < 5e-6          # the xlsx prints 6 digits
+
+
+def test_cut_upload_path_equals_device_preprocessing(ctx):
+    """pb_cut_upload with the host-side user data gives the same system as pb_cut_preprocess."""
+    N, k = 12, 1
+    gpu_cut_mesh(ctx, N, 4)
+    ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+    a = ctx.csr()
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=4)
+    ci = m.cut_info()
+    ctx.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT)
+    ctx.set_points(m.points())
+    ctx.cut_levelset(0, 0.35, 0.5, 0.5)
+    ctx.cut_upload(ci["node_loc"], ci["face_loc"], ci["face_ip"], ci["cell_loc"], ci["iface_off"], ci["iface_pts"])
+    ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+    b = ctx.csr()
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def test_cut_k3_is_refused(ctx):
+    """the Dunavant table has no rule for degree 8, the reference has no valid answer at k = 3."""
+    gpu_cut_mesh(ctx, 10, 4)
+    with pytest.raises(pb.ProtonError, match="k <= 2|no kernel instance"):
+        ctx.assemble(pb.hho_degree_info(4, 3), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
