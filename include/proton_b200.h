@@ -115,6 +115,21 @@ pb_status pb_recover(pb_ctx* ctx, double* full_solution);
  * for PB_PROBLEM_HHO; out[0] = H1 error^2 of cuthho_square.cpp:1031-1050 for PB_PROBLEM_FICTDOM */
 pb_status pb_error_norms(pb_ctx* ctx, double out[3]);
 
+/* ---- multi-GPU: one context per rank, 1-D strip partition by cell rows.  The reference is a single
+ * serial process; these entry points have no counterpart there.  Stages 1+2 need no communication (every rank also
+ * assembles the ghost row of cells below its strip).  The solve exchanges one halo of (2Nx-1)*fbs doubles with each
+ * neighbour per SpMV and all-reduces 1 + 2 scalars per iteration over NCCL (loaded with dlopen at pb_dist_init, so
+ * the library has no link-time NCCL dependency).
+ * pb_strip_layout is pure host arithmetic (works without a GPU): out = { first owned compressed face, one past the
+ * last, first / one-past-last compressed face referenced by the owned rows, first local cell row, owned scalar
+ * rows, lower halo doubles, upper halo doubles }. ---- */
+pb_status pb_strip_layout(long long Nx, long long Ny, long long row_begin, long long row_end, int fbs, long long out[8]);
+pb_status pb_dist_unique_id(unsigned char id[128]);
+pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsigned char id[128]);
+/* back-substitution on a strip: cell dofs of the OWNED cell rows only ([row_begin,row_end) x Nx x cbs) and the owned
+ * face dofs */
+pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
+
 /* ---- measurement hooks (bench.py): device-side timing of the last pb_assemble / pb_pcg, milliseconds ---- */
 pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg);
 /* register-resident DFMA peak probe (FP64 roofline denominator), TFLOP/s */

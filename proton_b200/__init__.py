@@ -5,6 +5,6 @@ proton_b200/csrc/Makefile).  There is no CPU implementation behind it: importing
 symbol table can be checked), every compute call needs a CUDA device and raises otherwise.
 """
 from ._binding import (PB, Context, ProtonError, abi_symbols, cg_params, hho_degree_info, lib, lib_path,
-                       mesh_init_params)
+                       mesh_init_params, strip_layout, strip_rows, dist_unique_id)
 
-__all__ = ["PB", "Context", "ProtonError", "abi_symbols", "cg_params", "hho_degree_info", "lib", "lib_path", "mesh_init_params"]
+__all__ = ["PB", "Context", "ProtonError", "abi_symbols", "cg_params", "hho_degree_info", "lib", "lib_path", "mesh_init_params", "strip_layout", "strip_rows", "dist_unique_id"]

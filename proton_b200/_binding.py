@@ -70,6 +70,31 @@ def lib():
     return _lib
 
 
+def strip_layout(Nx, Ny, row_begin, row_end, fbs):
+    """pb_strip_layout: host arithmetic of the 1-D strip partition (no GPU needed)."""
+    out = (C.c_longlong * 8)()
+    rc = lib().pb_strip_layout(C.c_longlong(Nx), C.c_longlong(Ny), C.c_longlong(row_begin), C.c_longlong(row_end), int(fbs), out)
+    if rc != PB.OK:
+        raise ProtonError(f"pb_strip_layout: invalid arguments ({Nx}, {Ny}, {row_begin}, {row_end}, {fbs})")
+    keys = ("cf_begin", "cf_end", "col_lo", "col_hi", "cell_row0", "n_rows", "halo_lo", "halo_hi")
+    return dict(zip(keys, [int(v) for v in out]))
+
+
+def strip_rows(Ny, world, rank):
+    """cell rows [begin, end) of `rank`: as even as possible, lower ranks take the remainder"""
+    base, rem = divmod(Ny, world)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+def dist_unique_id():
+    buf = (C.c_ubyte * 128)()
+    rc = lib().pb_dist_unique_id(buf)
+    if rc != PB.OK:
+        raise ProtonError(lib().pb_last_error(None).decode())
+    return bytes(buf)
+
+
 class mesh_init_params:
     def __init__(self, Nx=4, Ny=4, min_x=0.0, max_x=1.0, min_y=0.0, max_y=1.0):
         self.Nx, self.Ny, self.min_x, self.max_x, self.min_y, self.max_y = Nx, Ny, min_x, max_x, min_y, max_y
@@ -135,6 +160,17 @@ class Context:
         self.nfaces = 2 * mip.Nx * mip.Ny + mip.Nx + mip.Ny
         self.ncells = mip.Nx * mip.Ny
         return self
+
+    def dist_init(self, rank, world, unique_id):
+        buf = (C.c_ubyte * 128).from_buffer_copy(unique_id)
+        self._ck(lib().pb_dist_init(self._h, int(rank), int(world), buf))
+        self.rank, self.world = rank, world
+
+    def recover_strip(self, row_begin, row_end):
+        """(cell dofs of the owned cell rows, owned face dofs)"""
+        cells = np.zeros((row_end - row_begin) * self.mip.Nx * self.hdi.cbs); faces = np.zeros(self.n_rows)
+        self._ck(lib().pb_recover_strip(self._h, _ptr(cells), _ptr(faces)))
+        return cells, faces
 
     def points(self):
         xy = np.zeros((self.npoints, 2)); self._ck(lib().pb_mesh_get_points(self._h, _ptr(xy))); return xy

@@ -45,6 +45,9 @@ struct pb_ctx {
     // solver
     double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
+    double *dfull = nullptr, *scal = nullptr;      // d with halos (d = dfull + halo_lo); all-reduced scalars
+    // multi-GPU
+    int rank = 0, world = 1; void* comm = nullptr;
     // timings
     cudaEvent_t ev[4]{};
     double ms_local = 0, ms_scatter = 0, ms_pcg = 0;
@@ -134,10 +137,11 @@ extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
-    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->d); dfree(&c->y); dfree(&c->iA); dfree(&c->parts);
+    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->parts); dfree(&c->scal);
     c->assembled = false;
 }
 
+static void dist_release(pb_ctx* c);      // pb_api_dist.inl
 static void free_cut(pb_ctx* c) {
     dfree(&c->node_loc); dfree(&c->face_loc); dfree(&c->cell_loc_g); dfree(&c->cut_cells); dfree(&c->face_ip); dfree(&c->iface);
     c->have_cut = false; c->ncut = 0; c->NI = 0;
@@ -147,6 +151,7 @@ extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     if (!ctx) return PB_OK;
     cudaSetDevice(ctx->device);
     free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->cg);
+    dist_release(ctx);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx; return PB_OK;
@@ -400,60 +405,6 @@ extern "C" pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, l
 }
 
 // ------------------------------------------------------------------------------------------------ stage 3
-static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 ? 8 : len <= 24 ? 8 : 16; }
-
-extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res) {
-    if (!ctx) return PB_ERR_INVALID;
-    NEED(ctx->assembled && p, PB_ERR_STATE, "pb_pcg: nothing assembled");
-    NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED,
-         "pb_pcg: this context owns a strip; the multi-rank solve is driven through pb_pcg_* step calls");
-    CK(cudaSetDevice(ctx->device));
-    const long long n = ctx->nrows;
-    if (!ctx->x) {
-        CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
-        CK(dalloc(ctx, &ctx->d, (size_t)n)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
-        CK(dalloc(ctx, &ctx->parts, (size_t)3 * PCG_MAX_BLOCKS));
-    }
-    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
-    int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
-    long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
-    double *p_dy = ctx->parts, *p_rr = ctx->parts + PCG_MAX_BLOCKS, *p_rz = ctx->parts + 2 * PCG_MAX_BLOCKS;
-    const int pre = p->apply_preconditioner ? 1 : 0;
-    const int lpr = spmv_lanes(ctx->F);
-    auto t0 = std::chrono::steady_clock::now();
-    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-    pcg_diag_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
-    pcg_init_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
-    pcg_init_state_kernel<<<1, PCG_THREADS, 0, ctx->stream>>>(nblk, p_rr, p_rz, ctx->cg);
-    CK(cudaGetLastError());
-    CgState hs{}; long long it = 0; const long long check_every = 32;
-    while (true) {
-        for (long long k = 0; k < check_every; k++, it++) {
-            if (it > 0) {
-                pcg_dir_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, nblk, p_rr, p_rz, ctx->z, ctx->d, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
-                pcg_commit_kernel<<<1, PCG_THREADS, 0, ctx->stream>>>(nblk, p_rr, p_rz, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
-            }
-            switch (lpr) {
-            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
-            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
-            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, 0, ctx->rowptr, ctx->col, ctx->val, ctx->d, 0, ctx->y, p_dy, ctx->cg); break;
-            }
-            pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, ctx->stream>>>(n, pre, nblk, p_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
-        }
-        CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        if (hs.done) break;
-    }
-    CK(cudaEventRecord(ctx->ev[1], ctx->stream)); CK(cudaStreamSynchronize(ctx->stream));
-    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
-    if (res) {
-        res->iterations = hs.iters; res->relative_residual = hs.relres; res->exit_reason = hs.reason;
-        res->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    }
-    return PB_OK;
-}
-
 extern "C" pb_status pb_get_face_solution(pb_ctx* ctx, double* x) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && x, PB_ERR_STATE, "pb_get_face_solution: no solution");
@@ -528,25 +479,7 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
     }
 }
 
-extern "C" pb_status pb_recover(pb_ctx* ctx, double* full) {
-    if (!ctx) return PB_ERR_INVALID;
-    NEED(ctx->assembled && ctx->x && full, PB_ERR_STATE, "pb_recover: no face solution");
-    NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_recover: whole-mesh contexts only");
-    CK(cudaSetDevice(ctx->device));
-    const long long ncg = ctx->ncells_global; const int C = ctx->C;
-    double* uc = nullptr; CK(cudaMalloc((void**)&uc, (size_t)ncg * C * 8));
-#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(ctx->grid, ctx->strip.cell_row0, ctx->ncells_local, ctx->grid.row_begin, C, ctx->prm.fun, \
-        ctx->points, ctx->recA, ctx->recb, ctx->x, 0, uc)
-    switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; case 2: PB_REC(2); break; case 3: PB_REC(3); break;
-    default: cudaFree(uc); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_recover: face degree %d", ctx->FD); }
-#undef PB_REC
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(full, uc, (size_t)ncg * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(full + ncg * C, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    cudaFree(uc);
-    return PB_OK;
-}
+#include "pb_api_dist.inl"
 
 extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
     if (!ctx) return PB_ERR_INVALID;

@@ -1,0 +1,220 @@
+// C ABI, solver part (included by pb_api.cu): strip layout, NCCL plumbing (dlopen), the PCG driver for one rank or a
+// row of ranks, back-substitution.
+#include <dlfcn.h>
+
+// ---- minimal NCCL surface, resolved at run time: the process that drives several ranks has already loaded NCCL
+// (torch.distributed), a single-rank user never needs it
+namespace nccl_dl {
+typedef struct { char internal[128]; } UniqueId;
+typedef void* Comm;
+enum { Sum = 0, Float64 = 8 };
+struct Api {
+    void* lib = nullptr;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(Comm*, int, UniqueId, int) = nullptr;
+    int (*CommDestroy)(Comm) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+static Api g;
+static bool load(std::string& why) {
+    if (g.lib) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) { g.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (g.lib) break; }
+    if (!g.lib) { why = std::string("cannot load NCCL: ") + dlerror(); return false; }
+#define PB_SYM(field, name) *(void**)(&g.field) = dlsym(g.lib, name); if (!g.field) { why = std::string("NCCL symbol missing: ") + name; g.lib = nullptr; return false; }
+    PB_SYM(GetUniqueId, "ncclGetUniqueId") PB_SYM(CommInitRank, "ncclCommInitRank") PB_SYM(CommDestroy, "ncclCommDestroy")
+    PB_SYM(AllReduce, "ncclAllReduce") PB_SYM(Send, "ncclSend") PB_SYM(Recv, "ncclRecv") PB_SYM(GroupStart, "ncclGroupStart")
+    PB_SYM(GroupEnd, "ncclGroupEnd") PB_SYM(GetErrorString, "ncclGetErrorString")
+#undef PB_SYM
+    return true;
+}
+}  // namespace nccl_dl
+#define NCK(call) do { int r_ = (call); if (r_ != 0) return fail(ctx, PB_ERR_CUDA, "%s failed: %s", #call, nccl_dl::g.GetErrorString(r_)); } while (0)
+
+static void dist_release(pb_ctx* c) { if (c->comm && nccl_dl::g.CommDestroy) nccl_dl::g.CommDestroy(c->comm); c->comm = nullptr; }
+
+extern "C" pb_status pb_strip_layout(long long Nx, long long Ny, long long row_begin, long long row_end, int fbs, long long out[8]) {
+    if (!out || Nx < 2 || Ny < 2 || fbs < 1 || row_begin < 0 || row_begin >= row_end || row_end > Ny) return PB_ERR_INVALID;
+    Grid g{}; g.Nx = Nx; g.Ny = Ny;
+    const long long nfree = num_free_faces(g);
+    const long long cf_begin = compress_row_start(g, row_begin), cf_end = row_end == Ny ? nfree : compress_row_start(g, row_end);
+    const long long cell_row0 = row_begin > 0 ? row_begin - 1 : 0;
+    const long long col_lo = compress_row_start(g, cell_row0);
+    long long col_hi = row_end == Ny ? nfree : compress_row_start(g, row_end) + (2 * Nx - 1);
+    if (col_hi > nfree) col_hi = nfree;
+    out[0] = cf_begin; out[1] = cf_end; out[2] = col_lo; out[3] = col_hi; out[4] = cell_row0;
+    out[5] = (cf_end - cf_begin) * fbs; out[6] = (cf_begin - col_lo) * fbs; out[7] = (col_hi - cf_end) * fbs;
+    return PB_OK;
+}
+
+extern "C" pb_status pb_dist_unique_id(unsigned char id[128]) {
+    pb_ctx* ctx = nullptr;
+    std::string why;
+    if (!id) return fail(nullptr, PB_ERR_INVALID, "pb_dist_unique_id: null output");
+    if (!nccl_dl::load(why)) return fail(nullptr, PB_ERR_CUDA, "pb_dist_unique_id: %s", why.c_str());
+    nccl_dl::UniqueId u;
+    NCK(nccl_dl::g.GetUniqueId(&u));
+    memcpy(id, u.internal, 128);
+    return PB_OK;
+}
+
+extern "C" pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsigned char id[128]) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(world >= 1 && rank >= 0 && rank < world && id, PB_ERR_INVALID, "pb_dist_init: bad rank / world / id");
+    CK(cudaSetDevice(ctx->device));
+    ctx->rank = rank; ctx->world = world;
+    if (world == 1) return PB_OK;
+    std::string why;
+    if (!nccl_dl::load(why)) return fail(ctx, PB_ERR_CUDA, "pb_dist_init: %s", why.c_str());
+    nccl_dl::UniqueId u; memcpy(u.internal, id, 128);
+    NCK(nccl_dl::g.CommInitRank(&ctx->comm, world, u, rank));
+    return PB_OK;
+}
+
+// ---- halo exchange of a face vector stored for the columns [col_lo, col_hi): `full` points at col_lo, the owned part
+// starts `down` doubles in and has n entries.  Rank r-1 needs my first face-row part (its upper halo: the faces
+// through h(., row_begin)), rank r+1 needs my last face row (its lower halo).
+static pb_status halo_exchange(pb_ctx* ctx, double* full) {
+    if (ctx->world == 1) return PB_OK;
+    const Grid& g = ctx->grid; const Strip& s = ctx->strip; const int F = ctx->F;
+    const long long n = ctx->nrows, down = (s.cf_begin - s.col_lo) * F, up = (s.col_hi - s.cf_end) * F;
+    const long long nfree = num_free_faces(g);
+    long long to_prev = s.cf_begin + (2 * g.Nx - 1); if (to_prev > nfree) to_prev = nfree;
+    to_prev = (to_prev - s.cf_begin) * F;                                       // upper halo of rank r-1
+    const long long to_next = (s.cf_end - compress_row_start(g, g.row_end - 1)) * F;   // lower halo of rank r+1: my last face row
+    double* own = full + down;
+    NCK(nccl_dl::g.GroupStart());
+    if (ctx->rank > 0) {
+        NCK(nccl_dl::g.Send(own, (size_t)to_prev, nccl_dl::Float64, ctx->rank - 1, ctx->comm, ctx->stream));
+        NCK(nccl_dl::g.Recv(full, (size_t)down, nccl_dl::Float64, ctx->rank - 1, ctx->comm, ctx->stream));
+    }
+    if (ctx->rank < ctx->world - 1) {
+        NCK(nccl_dl::g.Send(own + n - to_next, (size_t)to_next, nccl_dl::Float64, ctx->rank + 1, ctx->comm, ctx->stream));
+        NCK(nccl_dl::g.Recv(own + n, (size_t)up, nccl_dl::Float64, ctx->rank + 1, ctx->comm, ctx->stream));
+    }
+    NCK(nccl_dl::g.GroupEnd());
+    return PB_OK;
+}
+
+static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 ? 8 : len <= 24 ? 8 : 16; }
+
+// conjugated_gradient (solver_cg.hpp:63-144) on the condensed system of this context, or of the row of contexts that
+// share a communicator: same update order, exit tests and iteration count; dot products are all-reduced.
+extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && p, PB_ERR_STATE, "pb_pcg: nothing assembled");
+    const bool whole = ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid);
+    NEED(whole || (ctx->world > 1 && ctx->comm), PB_ERR_STATE, "pb_pcg: this context owns a strip: call pb_dist_init on every rank first");
+    CK(cudaSetDevice(ctx->device));
+    const long long n = ctx->nrows; const int F = ctx->F;
+    const long long xoff = ctx->strip.col_lo * F, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F, nfull = (ctx->strip.col_hi - ctx->strip.col_lo) * F;
+    if (!ctx->x) {
+        CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
+        CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
+        CK(dalloc(ctx, &ctx->parts, (size_t)3 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
+        CK(cudaMemsetAsync(ctx->dfull, 0, (size_t)nfull * 8, ctx->stream));
+    }
+    ctx->d = ctx->dfull + down;
+    const bool multi = ctx->world > 1;
+    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
+    int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
+    long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
+    double *p_dy = ctx->parts, *p_rr = ctx->parts + PCG_MAX_BLOCKS, *p_rz = ctx->parts + 2 * PCG_MAX_BLOCKS;
+    double *s_dy = ctx->scal, *s_rr = ctx->scal + 1, *s_rz = ctx->scal + 2;
+    // what the consuming kernels read: the per-block partials (one rank) or the all-reduced scalars (several)
+    const double *c_dy = multi ? s_dy : p_dy, *c_rr = multi ? s_rr : p_rr, *c_rz = multi ? s_rz : p_rz;
+    const int c_n = multi ? 1 : nblk;
+    const int pre = p->apply_preconditioner ? 1 : 0;
+    const int lpr = spmv_lanes(F);
+    cudaStream_t sm = ctx->stream;
+    auto reduce_rr_rz = [&]() -> pb_status {
+        if (!multi) return PB_OK;
+        pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk, p_rr, s_rr, p_rz, s_rz);
+        NCK(nccl_dl::g.AllReduce(s_rr, s_rr, 2, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
+        return PB_OK;
+    };
+    auto t0 = std::chrono::steady_clock::now();
+    CK(cudaEventRecord(ctx->ev[0], sm));
+    pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
+    pcg_init_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
+    { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
+    pcg_init_state_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, ctx->cg);
+    CK(cudaGetLastError());
+    CgState hs{}; long long it = 0; const long long check_every = 32;
+    while (true) {
+        for (long long k = 0; k < check_every; k++, it++) {
+            if (it > 0) {
+                pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, ctx->z, ctx->d, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+                pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+            }
+            { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
+            switch (lpr) {
+            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+            }
+            if (multi) {
+                pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk, p_dy, s_dy, nullptr, nullptr);
+                NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
+            }
+            pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, c_n, c_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
+            { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
+        }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, sm));
+        CK(cudaStreamSynchronize(sm));
+        if (hs.done) break;
+    }
+    CK(cudaEventRecord(ctx->ev[1], sm)); CK(cudaStreamSynchronize(sm));
+    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
+    if (res) {
+        res->iterations = hs.iters; res->relative_residual = hs.relres; res->exit_reason = hs.reason;
+        res->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return PB_OK;
+}
+
+// back-substitution (K6) for the owned cell rows; xfull = face solution for the columns [col_lo, col_hi)
+static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host) {
+    const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;
+    const long long n = ctx->nrows, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F, nfull = (ctx->strip.col_hi - ctx->strip.col_lo) * F;
+    const long long owned_cells = (g.row_end - g.row_begin) * g.Nx;
+    double *xfull = nullptr, *uc = nullptr;
+    CK(cudaMalloc((void**)&xfull, (size_t)nfull * 8)); CK(cudaMalloc((void**)&uc, (size_t)owned_cells * C * 8));
+    CK(cudaMemsetAsync(xfull, 0, (size_t)nfull * 8, ctx->stream));
+    CK(cudaMemcpyAsync(xfull + down, ctx->x, (size_t)n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    { pb_status st = halo_exchange(ctx, xfull); if (st != PB_OK) return st; }
+    double* uc_shift = uc - g.row_begin * g.Nx * C;          // the kernel indexes cell dofs by GLOBAL cell id
+#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, ctx->strip.cell_row0, ctx->ncells_local, g.row_begin, C, ctx->prm.fun, \
+        ctx->points, ctx->recA, ctx->recb, xfull, ctx->strip.col_lo * F, uc_shift)
+    switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; case 2: PB_REC(2); break; case 3: PB_REC(3); break;
+    default: cudaFree(uc); cudaFree(xfull); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_recover: face degree %d", ctx->FD); }
+#undef PB_REC
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(cell_dofs_host, uc, (size_t)owned_cells * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(uc); cudaFree(xfull);
+    return PB_OK;
+}
+
+extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && cell_dofs, PB_ERR_STATE, "pb_recover_strip: no face solution");
+    CK(cudaSetDevice(ctx->device));
+    pb_status st = recover_owned(ctx, cell_dofs); if (st != PB_OK) return st;
+    if (face_dofs) CK(cudaMemcpy(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
+    return PB_OK;
+}
+
+// the reference's FULL solution vector (cell dofs c*cbs+i, then face dofs cbs*ncells + compress[f]*fbs + a)
+extern "C" pb_status pb_recover(pb_ctx* ctx, double* full) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && full, PB_ERR_STATE, "pb_recover: no face solution");
+    NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_recover: whole-mesh contexts only (strips: pb_recover_strip)");
+    return pb_recover_strip(ctx, full, full + ctx->ncells_global * ctx->C);
+}

@@ -50,6 +50,14 @@ PB_D double reduce_partials(const double* parts, int nparts, double* sh) {
     return r;
 }
 
+// multi-rank runs: fold the per-block partials into one scalar per quantity so that the rank sums can be all-reduced
+__global__ void pcg_sum_partials_kernel(int nparts, const double* a, double* out_a, const double* b, double* out_b) {
+    __shared__ double sh[32];
+    double va = reduce_partials(a, nparts, sh);
+    if (threadIdx.x == 0) *out_a = va;
+    if (b) { double vb = reduce_partials(b, nparts, sh); if (threadIdx.x == 0) *out_b = vb; }
+}
+
 // iA = 1/diag(A) (solver_cg.hpp:78-81); A is scalar CSR with global column ids, rows [row0, row0+n)
 __global__ void pcg_diag_kernel(long long n, long long row0, const long long* __restrict__ rowptr, const int* __restrict__ col,
                                 const double* __restrict__ val, double* __restrict__ iA) {

@@ -1,0 +1,52 @@
+"""Multi-GPU check, launched by torchrun (one rank per GPU):
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/dist_gpu_check.py
+Every rank assembles its strip, the ranks solve together (NCCL halo exchange + all-reduces inside the library), and
+rank 0 compares the gathered solution with a whole-mesh single-GPU solve of the same problem."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import proton_b200 as pb
+from proton_b200 import PB
+from proton_b200.dist import make_rank_context
+
+
+def main():
+    rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    ok = True
+    for (Nx, Ny, k) in [(16, 16, 1), (24, 19, 2), (12, 32, 0)]:
+        mip = pb.mesh_init_params(Nx, Ny)
+        hdi = pb.hho_degree_info(k + 1, k)
+        ctx = make_rank_context(mip, PB.QUAD_TENSOR_GAUSS, rank, world, lr, dist)
+        ctx.assemble(hdi)
+        res = ctx.conjugated_gradient(pb.cg_params(1e-13, 100.0, 10000, True))
+        cells, faces = ctx.recover_strip(ctx.row_begin, ctx.row_end)
+        gc = [None] * world; gf = [None] * world
+        dist.all_gather_object(gc, cells); dist.all_gather_object(gf, faces)
+        if rank == 0:
+            ref = pb.Context(lr)
+            ref.mesh(mip).assemble(hdi)
+            r1 = ref.conjugated_gradient(pb.cg_params(1e-13, 100.0, 10000, True))
+            full = ref.recover()
+            got = np.concatenate(gc + gf)
+            err = np.linalg.norm(got - full) / np.linalg.norm(full)
+            print(f"N={Nx}x{Ny} k={k} world={world}: iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, rel diff {err:.2e}", flush=True)
+            ok = ok and err < 1e-9 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2
+            ref.close()
+        ctx.close()
+    flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    if rank == 0:
+        print("DIST CHECK", "PASSED" if ok else "FAILED", flush=True)
+    sys.exit(0 if int(flag) else 1)
+
+
+if __name__ == "__main__":
+    main()

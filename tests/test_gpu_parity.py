@@ -155,3 +155,28 @@ def test_distorted_quads(ctx):
     lc = ctx.local(PB.LOCAL_LC)
     worst = max(frob_rel(lc[c], (lambda r: r["data"] + r["stab"])(m.local(c, k + 1, k))) for c in range(m.ncells))
     assert worst < TOL_LOCAL, worst
+
+
+@pytest.mark.parametrize("k,Nx,Ny,cuts", [(1, 8, 8, (0, 4, 8)), (2, 7, 9, (0, 2, 5, 9)), (0, 6, 6, (0, 1, 6))])
+def test_strip_contexts_assemble_the_same_rows(k, Nx, Ny, cuts):
+    """multi-GPU partition, stages 1+2: every strip (with its ghost cell row) reproduces its rows of the whole-mesh
+    system bit for bit, without communication."""
+    hdi = pb.hho_degree_info(k + 1, k)
+    whole = pb.Context(0)
+    whole.mesh(pb.mesh_init_params(Nx, Ny)).assemble(hdi)
+    rp, col, val, rhs = whole.csr()
+    for rb, re in zip(cuts[:-1], cuts[1:]):
+        c = pb.Context(0)
+        c.mesh(pb.mesh_init_params(Nx, Ny), row_begin=rb, row_end=re).assemble(hdi)
+        L = pb.strip_layout(Nx, Ny, rb, re, hdi.fbs)
+        assert c.n_rows == L["n_rows"]
+        rp_s, col_s, val_s, rhs_s = c.csr()
+        r0 = L["cf_begin"] * hdi.fbs
+        lo, hi = rp[r0], rp[r0 + c.n_rows]
+        assert np.array_equal(rp_s, rp[r0 : r0 + c.n_rows + 1] - lo)
+        assert np.array_equal(col_s, col[lo:hi])
+        assert np.array_equal(val_s, val[lo:hi])
+        assert np.array_equal(rhs_s, rhs[r0 : r0 + c.n_rows])
+        assert col_s.min() >= L["col_lo"] * hdi.fbs and col_s.max() < L["col_hi"] * hdi.fbs
+        c.close()
+    whole.close()
