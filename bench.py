@@ -119,8 +119,9 @@ def run_ours(args, rank, world, local_rank):
     k, N = args.k, args.N
     Nx, Ny = N, N * world                      # weak scaling: every rank owns an N x N strip of an N x (N*world) mesh
     hdi = pb.hho_degree_info(k + 1, k)
-    ctx = pb.Context(dev)
-    ctx.mesh(pb.mesh_init_params(Nx, Ny, 0.0, 1.0, 0.0, float(world)), PB.QUAD_TENSOR_GAUSS, row_begin=rank * N, row_end=(rank + 1) * N)
+    from proton_b200.dist import make_rank_context
+    ctx = make_rank_context(pb.mesh_init_params(Nx, Ny, 0.0, 1.0, 0.0, float(world)), PB.QUAD_TENSOR_GAUSS, rank, world, dev, dist)
+    assert (ctx.row_begin, ctx.row_end) == (rank * N, (rank + 1) * N)
     fp64_peak = ctx.probe_fp64_peak()
     cells_rank = N * N                         # owned cells (the ghost row assembled for the strip's bottom faces is not counted)
 
@@ -164,24 +165,35 @@ def run_ours(args, rank, world, local_rank):
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     checksum = float(rhs_host.sum())
 
-    # ---------------- stage 3: PCG on the condensed system (single-rank contexts; see DESIGN.md for the multi-rank plan)
-    cg = None
-    if world == 1:
-        hbm, hbm_src = peaks()
-        spmv_bytes = 12.0 * nnz + 20.0 * n_rows
-        iter_bytes = spmv_bytes + 11 * 8.0 * n_rows                 # + vector passes of the dir / xrz kernels
+    # ---------------- stage 3: PCG on the condensed system (all ranks together: NCCL halo exchange + all-reduces)
+    hbm, hbm_src = peaks()
+    nnz_all, rows_all = nnz, n_rows
+    if dist is not None:
+        tt = torch.tensor([nnz, n_rows], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt); nnz_all, rows_all = int(tt[0]), int(tt[1])
+    spmv_bytes = 12.0 * nnz + 20.0 * n_rows                     # SURVEY §8d, this rank
+    iter_bytes = spmv_bytes + 11 * 8.0 * n_rows                 # + vector passes of the dir / xrz kernels
+    r_tol = t_tol = None
+    if world == 1 and not args.no_cg_tol:
         ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))          # warm-up + the reference's own problem
         r_tol = ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))
         t_tol = ctx.timings()["ms_pcg"]
-        fixed = 200
-        r_fix = ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, fixed, True))            # fixed-iteration run for bandwidth
-        t_fix = ctx.timings()["ms_pcg"]
-        its = r_fix["iterations"] + 1
-        ms_it = t_fix / its
-        cg = {"unknowns": n_rows, "nnz": nnz, "tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": t_tol,
-              "fixed_iterations": its, "ms_per_iter": ms_it, "iter_bytes": iter_bytes,
-              "roofline": {"bound": "hbm", "achieved": iter_bytes / (ms_it * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-                           "frac": iter_bytes / (ms_it * 1e-3) / 1e9 / hbm, "peak_source": hbm_src, "traffic": None}}
+    fixed = 200
+    ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 40, True))
+    sync_all()
+    r_fix = ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, fixed, True))            # fixed-iteration run for bandwidth
+    t_fix = ctx.timings()["ms_pcg"]
+    if dist is not None:
+        tt = torch.tensor([t_fix], dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX); t_fix = float(tt[0])
+    its = r_fix["iterations"] + 1
+    ms_it = t_fix / its
+    gbs = iter_bytes / (ms_it * 1e-3) / 1e9                                          # per GPU
+    cg = {"unknowns": rows_all, "nnz": nnz_all, "fixed_iterations": its, "ms_per_iter": ms_it, "iter_bytes_per_gpu": iter_bytes,
+          "halo_doubles_per_neighbour": (2 * Nx - 1) * hdi.fbs, "allreduces_per_iter": 2 if world > 1 else 0,
+          "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU", "frac": gbs / hbm, "peak_source": hbm_src, "traffic": None}}
+    if r_tol is not None:
+        cg.update({"tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": t_tol})
 
     # ---------------- reduce over ranks (max time), print on rank 0
     if dist is not None:
@@ -229,6 +241,7 @@ def main():
     ap.add_argument("--ref-N", dest="ref_N", type=int, default=128)
     ap.add_argument("--cpu-N", dest="cpu_N", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cg-tol", action="store_true", help="skip the solve-to-tolerance run (fixed-iteration bandwidth run only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
