@@ -355,7 +355,7 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     }
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     const int F = ctx->F;
-    scatter_values_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
+    scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
     CK(cudaGetLastError());
     scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
     CK(cudaGetLastError());

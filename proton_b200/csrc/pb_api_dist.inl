@@ -131,6 +131,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     const int c_n = multi ? 1 : nblk;
     const int pre = p->apply_preconditioner ? 1 : 0;
     const int lpr = spmv_lanes(F);
+    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4;      // scalar-CSR product kept for comparison runs
     cudaStream_t sm = ctx->stream;
     auto reduce_rr_rz = [&]() -> pb_status {
         if (!multi) return PB_OK;
@@ -153,11 +154,17 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
                 pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
             }
             { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
-            switch (lpr) {
-            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+#define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->brows, ctx->brp, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg)
+            if (use_csr) {
+                switch (lpr) {
+                case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+                case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+                default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+                }
+            } else {
+                switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
             }
+#undef PB_SPMV
             if (multi) {
                 pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk, p_dy, s_dy, nullptr, nullptr);
                 NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));

@@ -8,6 +8,7 @@
 // order), so results are deterministic and no host round trip is needed inside an iteration.
 #pragma once
 #include "pb_device.cuh"
+#include "pb_system.cuh"
 
 namespace pb {
 
@@ -108,6 +109,57 @@ __global__ void pcg_spmv_kernel(long long n, long long xoff, const long long* __
 #pragma unroll
         for (int o = LPR / 2; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, LPR);
         if (sub == 0 && row < n) { y[row] = acc; dy += acc * dvec[down + row]; }
+    }
+    double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
+}
+
+// The same product on the implicit block structure: the F scalar rows of a free face share their column blocks, so the
+// column of entry k of a row is bcol[k / F] * F + k % F from the 56-byte BlockRow record of the face (cached, shared by
+// F rows) instead of a 4-byte index per entry from HBM: 8 + 64/F^2 bytes per non-zero instead of 12.  The value
+// array is the scalar CSR one (rows of a face are contiguous).  CS = 1 streams the values with evict-first loads;
+// measured slower (a 504-byte block row is consumed by one lane group over several instructions and needs L1 to merge
+// the partially used sectors), so CS = 0 is what runs.
+template <int LPR, int F, int CS>
+__global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow* __restrict__ rows, const long long* __restrict__ brp,
+                                    const double* __restrict__ val, const double* __restrict__ dvec, long long down,
+                                    double* __restrict__ y, double* __restrict__ parts_dy, const CgState* st) {
+    // one group of LPR lanes per BLOCK row: a lane gathers the vector entry of its columns once and feeds the F scalar
+    // rows of the face with it (F x fewer gathers, F independent value loads in flight per column)
+    __shared__ double sh[32];
+    if (st->done) return;
+    const int sub = threadIdx.x % LPR;
+    const long long nbr = n / F;
+    const long long groups = (long long)gridDim.x * blockDim.x / LPR;
+    const long long npass = (nbr + groups - 1) / groups;
+    double dy = 0.0;
+    long long br = (blockIdx.x * (long long)blockDim.x + threadIdx.x) / LPR;
+    for (long long pass = 0; pass < npass; pass++, br += groups) {
+        double acc[F];
+#pragma unroll
+        for (int a = 0; a < F; a++) acc[a] = 0.0;
+        if (br < nbr) {
+            const BlockRow* R = rows + br;
+            const int len = R->nb * F;
+            const double* v = val + brp[br] * (F * F);
+#pragma unroll
+            for (int t = 0; t < (7 * F + LPR - 1) / LPR; t++) {
+                const int k = sub + t * LPR;
+                if (k < len) {
+                    const int b = k / F, bc = k - b * F;
+                    const double xv = dvec[(long long)R->bcol[b] * F + bc - xoff];
+#pragma unroll
+                    for (int a = 0; a < F; a++) acc[a] += (CS ? __ldcs(v + a * len + k) : v[a * len + k]) * xv;
+                }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < F; a++)
+#pragma unroll
+            for (int o = LPR / 2; o > 0; o >>= 1) acc[a] += __shfl_down_sync(0xffffffffu, acc[a], o, LPR);
+        if (sub == 0 && br < nbr) {
+#pragma unroll
+            for (int a = 0; a < F; a++) { y[br * F + a] = acc[a]; dy += acc[a] * dvec[down + br * F + a]; }
+        }
     }
     double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
 }

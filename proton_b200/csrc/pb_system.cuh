@@ -84,35 +84,29 @@ __global__ void fill_csr_pattern_kernel(long long nrows_blk, int F, const BlockR
         for (int bc = 0; bc < F; bc++) col[base + b * F + bc] = R.bcol[b] * F + bc;
 }
 
-// values: one thread per scalar entry, grouped so that consecutive threads write consecutive CSR entries.
+// values: one warp per block row.  The F scalar rows of a block row are consecutive in the CSR arrays, so a block row
+// is one contiguous run of nb*F*F values: lanes walk it with unit stride (coalesced stores) and gather their <= 2 cell
+// contributions from the two S blocks of the face (1152 B each at k=2: L1/L2 hits after the first touch).
 // S is [cell][NF*NF] column-major (symmetric); entry (row li*F+a, col lj*F+bc).
-__global__ void scatter_values_kernel(long long nrows_blk, int F, const BlockRow* rows, const long long* brp,
+__global__ void scatter_values_kernel(long long nrows_blk, int F, const BlockRow* __restrict__ rows, const long long* __restrict__ brp,
                                       const double* __restrict__ S, double* __restrict__ val) {
-    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;   // scalar row
-    // thread layout: blockDim.x = 32 * k; each warp handles consecutive entries of consecutive rows
-    long long total_rows = nrows_blk * F;
-    // one warp per 32 consecutive entries would need a search; instead loop: each thread owns a scalar row and the
-    // warp cooperatively walks the rows of its 32-row window so that stores are contiguous.
-    int lane = threadIdx.x & 31;
-    long long row0 = t - lane;
+    const int lane = threadIdx.x & 31;
+    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
     const int NF = 4 * F;
-    for (int rr = 0; rr < 32; rr++) {
-        long long row = row0 + rr;
-        if (row >= total_rows) break;
-        long long br = row / F; int a = (int)(row - br * F);
-        const BlockRow& R = rows[br];
-        long long base = brp[br] * F * F + (long long)a * R.nb * F;
-        int len = R.nb * F;
+    for (long long br = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5; br < nrows_blk; br += nwarps) {
+        const BlockRow R = rows[br];
+        const int rowlen = R.nb * F, len = rowlen * F;
+        double* out = val + brp[br] * F * F;
+        const double* S0 = S + (long long)R.cell[0] * (NF * NF) + R.li[0] * F * NF;
+        const double* S1 = S + (long long)R.cell[1] * (NF * NF) + R.li[1] * F * NF;
         for (int e = lane; e < len; e += 32) {
-            int b = e / F, bc = e - b * F;
+            const int a = e / rowlen, rem = e - a * rowlen, b = rem / F, bc = rem - b * F;
+            const unsigned char l0 = R.src[0][b], l1 = R.src[1][b];
             double v = 0.0;
-#pragma unroll
-            for (int k = 0; k < 2; k++) {
-                unsigned char lj = R.src[k][b];
-                // S is symmetric up to rounding: read the transposed entry so that bc runs over contiguous doubles
-                if (lj != 255) v += S[(long long)R.cell[k] * (NF * NF) + (R.li[k] * F + a) * NF + lj * F + bc];
-            }
-            val[base + e] = v;
+            // S is symmetric up to rounding: read the transposed entry so that bc runs over contiguous doubles
+            if (l0 != 255) v += S0[a * NF + l0 * F + bc];
+            if (l1 != 255) v += S1[a * NF + l1 * F + bc];
+            out[e] = v;
         }
     }
 }
