@@ -112,7 +112,8 @@ pb_status pb_set_face_solution(pb_ctx* ctx, const double* x);
  * cbs*ncells + compress[f]*fbs + a), hho.hpp:362-379 */
 pb_status pb_recover(pb_ctx* ctx, double* full_solution);
 /* error norms of the drivers: out[0..2] = sums of squares of convergence_test.cpp:254-306 (L2, mass-norm, energy)
- * for PB_PROBLEM_HHO; out[0] = H1 error^2 of cuthho_square.cpp:1031-1050 for PB_PROBLEM_FICTDOM */
+ * for PB_PROBLEM_HHO; out[0] = H1 error^2 of cuthho_square.cpp:1031-1050 for PB_PROBLEM_FICTDOM.  A strip context
+ * returns the sums over its owned cells (add them over the ranks). */
 pb_status pb_error_norms(pb_ctx* ctx, double out[3]);
 
 /* ---- multi-GPU: one context per rank, 1-D strip partition by cell rows.  The reference is a single

@@ -12,6 +12,7 @@
 
 #include "pb_local.cuh"
 #include "pb_cut.cuh"
+#include "pb_norms.cuh"
 #include "pb_pcg.cuh"
 #include "pb_system.cuh"
 
@@ -480,12 +481,6 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
 }
 
 #include "pb_api_dist.inl"
-
-extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
-    if (!ctx) return PB_ERR_INVALID;
-    (void)out;
-    return fail(ctx, PB_ERR_UNSUPPORTED, "pb_error_norms: not built yet (SURVEY 8f.1)");
-}
 
 extern "C" pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg) {
     if (!ctx) return PB_ERR_INVALID;

@@ -187,7 +187,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
 }
 
 // back-substitution (K6) for the owned cell rows; xfull = face solution for the columns [col_lo, col_hi)
-static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host) {
+static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** keep_uc = nullptr, double** keep_xfull = nullptr) {
     const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;
     const long long n = ctx->nrows, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F, nfull = (ctx->strip.col_hi - ctx->strip.col_lo) * F;
     const long long owned_cells = (g.row_end - g.row_begin) * g.Nx;
@@ -203,9 +203,10 @@ static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host) {
     default: cudaFree(uc); cudaFree(xfull); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_recover: face degree %d", ctx->FD); }
 #undef PB_REC
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(cell_dofs_host, uc, (size_t)owned_cells * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (cell_dofs_host) CK(cudaMemcpyAsync(cell_dofs_host, uc, (size_t)owned_cells * C * 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    cudaFree(uc); cudaFree(xfull);
+    if (keep_uc) *keep_uc = uc; else cudaFree(uc);
+    if (keep_xfull) *keep_xfull = xfull; else cudaFree(xfull);
     return PB_OK;
 }
 
@@ -224,4 +225,42 @@ extern "C" pb_status pb_recover(pb_ctx* ctx, double* full) {
     NEED(ctx->assembled && ctx->x && full, PB_ERR_STATE, "pb_recover: no face solution");
     NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_recover: whole-mesh contexts only (strips: pb_recover_strip)");
     return pb_recover_strip(ctx, full, full + ctx->ncells_global * ctx->C);
+}
+
+// ---- K7: error norms of the drivers (pb_norms.cuh) over the owned cells; strips return partial sums
+template <int CD, int FD, int QK>
+static cudaError_t launch_norms_t(pb_ctx* c, NormArgs& A, int grid) {
+    const size_t smem = sizeof(NormSmem<CD, FD>);
+    auto kern = error_norms_kernel<CD, FD, QK>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, 32, smem, c->stream>>>(A);
+    return cudaGetLastError();
+}
+
+extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && out, PB_ERR_STATE, "pb_error_norms: no face solution");
+    CK(cudaSetDevice(ctx->device));
+    double *uc = nullptr, *xfull = nullptr;
+    pb_status st = recover_owned(ctx, nullptr, &uc, &xfull); if (st != PB_OK) return st;
+    const int grid = 148 * 16;
+    double* parts = nullptr; CK(cudaMalloc((void**)&parts, (size_t)grid * 3 * 8));
+    NormArgs A{};
+    A.grid = ctx->grid; A.points = ctx->points; A.ucell = uc; A.xfull = xfull; A.xoff = ctx->strip.col_lo * ctx->F;
+    A.fun = ctx->prm.fun; A.problem = ctx->prm.problem;
+    A.cell_loc_g = ctx->cell_loc_g; A.node_loc = ctx->node_loc; A.cut_cells = ctx->cut_cells; A.iface = ctx->iface; A.ncut = ctx->ncut; A.NI = ctx->NI;
+    A.parts = parts;
+    cudaError_t e = cudaErrorInvalidValue; const int cd = ctx->CD, fd = ctx->FD, qk = ctx->quad_kind;
+#define PB_NORM(CD_, FD_, QK_) if (cd == CD_ && fd == FD_ && qk == QK_) e = launch_norms_t<CD_, FD_, QK_>(ctx, A, grid);
+    PB_NORM(1, 0, 0) PB_NORM(2, 1, 0) PB_NORM(3, 2, 0) PB_NORM(4, 3, 0) PB_NORM(1, 0, 1) PB_NORM(2, 1, 1) PB_NORM(3, 2, 1)
+#undef PB_NORM
+    if (e != cudaSuccess) { cudaFree(parts); cudaFree(uc); cudaFree(xfull); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_error_norms: no kernel instance for HHO(%d,%d) quad_kind=%d (%s)", cd, fd, qk, cudaGetErrorString(e)); }
+    std::vector<double> h((size_t)grid * 3);
+    CK(cudaMemcpyAsync(h.data(), parts, h.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    out[0] = out[1] = out[2] = 0.0;
+    for (int b = 0; b < grid; b++) for (int k = 0; k < 3; k++) out[k] += h[3 * b + k];
+    cudaFree(parts); cudaFree(uc); cudaFree(xfull);
+    return PB_OK;
 }

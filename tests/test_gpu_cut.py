@@ -89,6 +89,8 @@ def test_fictdom_solution_and_golden_error(ctx, golden, k, N):
     assert frob_rel(full[:nT], sol[:nT]) < TOL_SOL
     e_gpu = S.error_fictdom(full); e_ref = S.error_fictdom(sol)
     assert abs(e_gpu - e_ref) / e_ref < TOL_SOL
+    e_dev = float(np.sqrt(ctx.error_norms()[0]))          # K7 on the device
+    assert abs(e_dev - e_ref) / e_ref < TOL_SOL, (e_dev, e_ref)
     key = f"k{k}_N{N}_r4"
     if key in golden["cuthho_fictdom"]:
         ref = golden["cuthho_fictdom"][key]

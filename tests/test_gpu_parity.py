@@ -105,6 +105,9 @@ def test_pcg_solution_matches_full_system_direct_solve(ctx, k, N):
     # error norms of convergence_test.cpp:254-306 evaluated by the oracle on the GPU solution
     e_gpu = np.sqrt(np.array(S.errors_convergence(full))); e_ref = np.sqrt(np.array(S.errors_convergence(sol)))
     assert np.max(np.abs(e_gpu - e_ref) / e_ref) < TOL_SOL
+    # the same norms computed on the device (K7, pb_error_norms)
+    e_dev = np.sqrt(ctx.error_norms())
+    assert np.max(np.abs(e_dev - e_ref) / e_ref) < TOL_SOL, (e_dev, e_ref)
 
 
 def test_pcg_iteration_count_matches_reference_cg(ctx):
