@@ -116,6 +116,20 @@ pb_status pb_recover(pb_ctx* ctx, double* full_solution);
  * returns the sums over its owned cells (add them over the ranks). */
 pb_status pb_error_norms(pb_ctx* ctx, double out[3]);
 
+/* ---- obstacle problem (apps/obstacle/obstacle.cpp:47-218): HHO(0, face_degree), face_degree in {0, 1}, full HHO
+ * stabilisation, load with quadrature increase `rhs_degree_increase` (the driver uses 1), data of obstacle.cpp:65-89 on
+ * the mesh the caller created (the driver uses [-1,1]^2).  The reference rebuilds make_obstacle_assembler(msh, in_A, hdi)
+ * + assemble(msh, cl, lc, f, gamma, bcs) (src/methods/hho_bits/hho.hpp:471-695) and solves the saddle system with
+ * SparseLU in every outer iteration, then expand_solution (:698-744).  Here the cell rows are eliminated in closed form
+ * (cell degree 0) and each outer iteration is condense -> scatter -> PCG -> update on cached local matrices.
+ * pb_obstacle_iterate performs ONE outer iteration (in_A from the current alpha, beta; solve; new alpha, beta) and
+ * returns ||alpha_prev - alpha|| (the driver's stopping quantity, obstacle.cpp:193), the size of the active set and
+ * the inner CG iterations.  pb_obstacle_error: the driver's final error^2 (obstacle.cpp:201-218). ---- */
+pb_status pb_obstacle_begin(pb_ctx* ctx, int face_degree, int rhs_degree_increase);
+pb_status pb_obstacle_iterate(pb_ctx* ctx, const pb_cg_params* cg, double* delta_alpha_norm, long long* n_active, long long* cg_iterations);
+pb_status pb_obstacle_error(pb_ctx* ctx, double* error_squared);
+pb_status pb_obstacle_get(pb_ctx* ctx, double* alpha_cells, double* beta, unsigned char* in_A);
+
 /* ---- multi-GPU: one context per rank, 1-D strip partition by cell rows.  The reference is a single
  * serial process; these entry points have no counterpart there.  Stages 1+2 need no communication (every rank also
  * assembles the ghost row of cells below its strip).  The solve exchanges one halo of (2Nx-1)*fbs doubles with each

@@ -256,5 +256,39 @@ class Context:
     def error_norms(self):
         out = np.zeros(3); self._ck(lib().pb_error_norms(self._h, _ptr(out))); return out
 
+    # ---- obstacle problem (apps/obstacle/obstacle.cpp)
+    def obstacle_begin(self, face_degree, rhs_degree_increase=1):
+        self._ck(lib().pb_obstacle_begin(self._h, int(face_degree), int(rhs_degree_increase)))
+        self.hdi = hho_degree_info(0, face_degree)
+        n = C.c_longlong(); nnz = C.c_longlong(); nc = C.c_longlong(); nl = C.c_longlong()
+        self._ck(lib().pb_system_sizes(self._h, C.byref(n), C.byref(nnz), C.byref(nc), C.byref(nl)))
+        self.n_rows, self.nnz, self.ncells_local, self.n_local = n.value, nnz.value, nc.value, nl.value
+
+    def obstacle_iterate(self, cgp):
+        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(bool(cgp.apply_preconditioner)))
+        d = C.c_double(); na = C.c_longlong(); it = C.c_longlong()
+        self._ck(lib().pb_obstacle_iterate(self._h, C.byref(p), C.byref(d), C.byref(na), C.byref(it)))
+        return d.value, na.value, it.value
+
+    def obstacle_error(self):
+        e = C.c_double(); self._ck(lib().pb_obstacle_error(self._h, C.byref(e))); return float(np.sqrt(e.value))
+
+    def obstacle_state(self):
+        a = np.zeros(self.ncells_local); b = np.zeros(self.ncells_local); ia = np.zeros(self.ncells_local, np.uint8)
+        self._ck(lib().pb_obstacle_get(self._h, _ptr(a), _ptr(b), _ptr(ia))); return a, b, ia
+
+    def obstacle_solve(self, face_degree, max_outer=50, tol=1e-7, cgp=None):
+        """the driver's loop (obstacle.cpp:119-198): returns (error, outer iterations, log)"""
+        cgp = cgp or cg_params(1e-13, 1e300, 100000, True)
+        self.obstacle_begin(face_degree, 1)
+        it, log = 0, []
+        while it < max_outer:
+            d, na, cgit = self.obstacle_iterate(cgp)
+            log.append((d, na, cgit))
+            if d < tol:
+                break
+            it += 1
+        return self.obstacle_error(), it, log
+
     def probe_fp64_peak(self):
         t = C.c_double(); self._ck(lib().pb_probe_fp64_peak(self._h, C.byref(t))); return t.value

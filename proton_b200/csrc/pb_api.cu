@@ -15,6 +15,8 @@
 #include "pb_norms.cuh"
 #include "pb_pcg.cuh"
 #include "pb_system.cuh"
+#include "pb_generic.cuh"
+#include "pb_obstacle.cuh"
 
 using namespace pb;
 
@@ -47,6 +49,8 @@ struct pb_ctx {
     double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
     double *dfull = nullptr, *scal = nullptr;      // d with halos (d = dfull + halo_lo); all-reduced scalars
+    // obstacle active-set state (per cell)
+    double *ob_alpha = nullptr, *ob_beta = nullptr, *ob_gamma = nullptr, *ob_xprev = nullptr; unsigned char* ob_inA = nullptr; bool ob_ready = false;
     // multi-GPU
     int rank = 0, world = 1; void* comm = nullptr;
     // timings
@@ -139,6 +143,7 @@ static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
     dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->parts); dfree(&c->scal);
+    dfree(&c->ob_alpha); dfree(&c->ob_beta); dfree(&c->ob_gamma); dfree(&c->ob_xprev); dfree(&c->ob_inA); c->ob_ready = false;
     c->assembled = false;
 }
 
@@ -313,6 +318,40 @@ static pb_status build_structure(pb_ctx* ctx) {
     return PB_OK;
 }
 
+template <int CD, int FD, int QK, int SK>
+static cudaError_t launch_generic_t(pb_ctx* c, const LocalArgs& A, int rhs_di) {
+    const size_t smem = sizeof(GenSmem<CD, FD>);
+    auto kern = local_generic_kernel<CD, FD, QK, SK>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    long long grid = A.ncells < 148 * 32 ? A.ncells : 148 * 32;
+    kern<<<(unsigned)grid, 32, smem, c->stream>>>(A, rhs_di);
+    return cudaGetLastError();
+}
+// every valid hho_degree_info that the tuned K1 has no instance for: equal order (k,k) and the obstacle's HHO(0,k)
+static pb_status launch_generic(pb_ctx* ctx, const LocalArgs& A, int cd, int fd, int qk, int sk, int rhs_di, bool* found) {
+    *found = true; cudaError_t e = cudaSuccess;
+#define PB_GEN(CD_, FD_) \
+    if (cd == CD_ && fd == FD_) { \
+        if (qk == 0 && sk == 1) e = launch_generic_t<CD_, FD_, 0, 1>(ctx, A, rhs_di); else if (qk == 0) e = launch_generic_t<CD_, FD_, 0, 0>(ctx, A, rhs_di); \
+        else if (sk == 1) e = launch_generic_t<CD_, FD_, 1, 1>(ctx, A, rhs_di); else e = launch_generic_t<CD_, FD_, 1, 0>(ctx, A, rhs_di); \
+        if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "local_generic_kernel launch failed: %s", cudaGetErrorString(e)); \
+        return PB_OK; }
+    PB_GEN(0, 0) PB_GEN(0, 1) PB_GEN(1, 1) PB_GEN(2, 2) PB_GEN(1, 2)
+#undef PB_GEN
+    *found = false; return PB_OK;
+}
+
+// K3: condensed blocks -> CSR values and rhs
+static pb_status scatter_system(pb_ctx* ctx) {
+    const int F = ctx->F;
+    scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
+    CK(cudaGetLastError());
+    scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
+    CK(cudaGetLastError());
+    return PB_OK;
+}
+
 extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->have_mesh && p, PB_ERR_STATE, "pb_assemble: no mesh");
@@ -350,16 +389,13 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     bool found = false;
     CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
+    if (!found) { pb_status st = launch_generic(ctx, A, cd, fd, ctx->quad_kind, sk, p->rhs_degree_increase, &found); if (st != PB_OK) return st; }
     if (!found) return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: no kernel instance for HHO(%d,%d) quad_kind=%d stab=%d load degree %d", cd, fd, ctx->quad_kind, p->stab_kind, rqd);
     if (p->problem == PB_PROBLEM_FICTDOM && ctx->ncut > 0) {
         pb_status st = launch_cut(ctx, A, cd, fd); if (st != PB_OK) return st;
     }
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-    const int F = ctx->F;
-    scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
-    CK(cudaGetLastError());
-    scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
-    CK(cudaGetLastError());
+    { pb_status st = scatter_system(ctx); if (st != PB_OK) return st; }
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_local = ms;
@@ -481,6 +517,7 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
 }
 
 #include "pb_api_dist.inl"
+#include "pb_api_obstacle.inl"
 
 extern "C" pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg) {
     if (!ctx) return PB_ERR_INVALID;
