@@ -11,7 +11,9 @@
 // views into the batch (assembler::local_contrib).  Errors are exceptions, like the reference (std::logic_error /
 // std::invalid_argument); there is no CPU fallback: without a CUDA device construction throws.
 #pragma once
+#include <cmath>
 #include <cstddef>
+#include <cstdio>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -80,6 +82,31 @@ public:
     size_t num_points() const { return (mip_.Nx + 1) * (mip_.Ny + 1); }
     std::vector<T> points() const { std::vector<T> xy(2 * num_points()); ck(ctx_, pb_mesh_get_points(ctx_, xy.data())); return xy; }
     void check(pb_status st) const { ck(ctx_, st); }
+    const mesh_init_params<T>& params() const { return mip_; }
+    // detect_node_position, detect_cut_faces, move_nodes, detect_cut_faces, detect_cut_cells, refine_interface
+    // (apps/cuthho/cuthho_square.cpp:2030-2052) for one of the reference's level sets, on the device
+    template <typename LevelSet>
+    void cut_preprocess(const LevelSet& ls, int refine_steps) {
+        ck(ctx_, pb_cut_levelset(ctx_, ls.kind(), ls.radius, ls.alpha, ls.beta, ls.cut_y));
+        ck(ctx_, pb_cut_preprocess(ctx_, refine_steps));
+    }
+};
+
+// level sets of apps/cuthho/cuthho_square.cpp:56-124: host-evaluable like the reference's functors; the device uses the
+// same formulas (pb_cut_levelset)
+template <typename T>
+struct circle_level_set {
+    T radius, alpha, beta, cut_y = 0;
+    circle_level_set(T r, T a, T b) : radius(r), alpha(a), beta(b) {}
+    int kind() const { return 0; }
+    T operator()(T x, T y) const { return (x - alpha) * (x - alpha) + (y - beta) * (y - beta) - radius * radius; }
+};
+template <typename T>
+struct line_level_set {
+    T radius = 0, alpha = 0, beta = 0, cut_y;
+    explicit line_level_set(T cy) : cut_y(cy) {}
+    int kind() const { return 1; }
+    T operator()(T, T y) const { return y - cut_y; }
 };
 
 // CSR view of assembler.LHS (the condensed face system; the reference's full system has no counterpart here)
@@ -128,6 +155,10 @@ public:
         return full;
     }
     const cartesian_mesh<T>& mesh() const { return msh_; }
+    // the drivers' post-processing sums: {L2^2, mass-norm^2, energy^2} (convergence_test.cpp:254-306) or {H1^2, 0, 0}
+    // for the fictitious-domain problem (cuthho_square.cpp:1031-1050)
+    std::vector<T> error_norms() const { std::vector<T> out(3); msh_.check(pb_error_norms(msh_.ctx(), out.data())); return out; }
+    size_t system_size() const { long long n = 0; msh_.check(pb_system_sizes(msh_.ctx(), &n, nullptr, nullptr, nullptr)); return (size_t)n; }
 };
 
 template <typename T>
@@ -144,6 +175,24 @@ cg_exit_reason conjugated_gradient(const assembler<T>& assm, std::vector<T>& x, 
     assm.mesh().check(pb_get_face_solution(assm.mesh().ctx(), x.data()));
     if (iterations) *iterations = (size_t)r.iterations;
     return r.exit_reason == PB_CG_CONVERGED ? cg_exit_reason::CONVERGED : r.exit_reason == PB_CG_DIVERGED ? cg_exit_reason::DIVERGED : cg_exit_reason::MAX_ITER_REACHED;
+}
+
+// run_hho_obstacle (apps/obstacle/obstacle.cpp:47-218): the active-set loop; returns the driver's error
+template <typename T>
+T run_hho_obstacle(const cartesian_mesh<T>& msh, size_t degree, size_t* outer_iterations = nullptr, bool verbose = true) {
+    msh.check(pb_obstacle_begin(msh.ctx(), (int)degree, 1));
+    pb_cg_params cg{1e-13, 1e300, 1000000, 1};
+    size_t iter = 0;
+    while (iter < 50) {
+        double delta = 0; long long na = 0, cgit = 0;
+        msh.check(pb_obstacle_iterate(msh.ctx(), &cg, &delta, &na, &cgit));
+        if (verbose) printf("Iteration %zu: active cells %lld, ||alpha_prev - alpha|| = %.6e, CG iterations %lld\n", iter + 1, na, delta, cgit);
+        if (delta < 1e-7) break;
+        iter++;
+    }
+    double e2 = 0; msh.check(pb_obstacle_error(msh.ctx(), &e2));
+    if (outer_iterations) *outer_iterations = iter;
+    return (T)std::sqrt(e2);
 }
 
 }  // namespace proton_b200

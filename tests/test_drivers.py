@@ -1,0 +1,60 @@
+"""The C++ drivers (apps/*.cpp over proton_host.hpp + the C ABI): they build, refuse to run without a GPU (no CPU
+fallback), and on a B200 print the reference's golden numbers."""
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "apps", "bin")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "apps"), "-s"])
+
+
+def _have_gpu():
+    import torch
+    return torch.cuda.is_available()
+
+
+def test_drivers_build_and_fail_loudly_without_gpu():
+    _build()
+    for exe in ("convergence_test", "cuthho_square", "obstacle"):
+        assert os.path.exists(os.path.join(BIN, exe))
+    if _have_gpu():
+        pytest.skip("GPU present")
+    r = subprocess.run([os.path.join(BIN, "obstacle"), "-k", "1", "-N", "8"], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_obstacle_driver_prints_reference_error(golden):
+    _build()
+    r = subprocess.run([os.path.join(BIN, "obstacle"), "-k", "1", "-N", "16"], capture_output=True, text=True, check=True)
+    err = float(re.search(r"Error: ([0-9.eE+-]+)", r.stdout).group(1))
+    ref = golden["obstacle"]["16"]["k1"]
+    assert abs(err - ref) / ref < 1e-5
+
+
+@pytest.mark.gpu
+def test_cuthho_square_driver_prints_reference_error(golden):
+    _build()
+    r = subprocess.run([os.path.join(BIN, "cuthho_square"), "-f", "-k", "1", "-M", "10", "-N", "10", "-r", "4"], capture_output=True, text=True, check=True)
+    err = float(re.search(r"H1-error : ([0-9.eE+-]+)", r.stdout).group(1))
+    ref = golden["cuthho_fictdom"]["k1_N10_r4"]
+    assert abs(err - ref) / ref < 5e-6
+
+
+@pytest.mark.gpu
+def test_convergence_test_driver_rates(tmp_path):
+    _build()
+    cfg = tmp_path / "cfg.lua"
+    cfg.write_text("-- flat config, the reference's keys\ndeg_min = 1\ndeg_max = 2\nmin_N = 8\nsteps = 3\nprecond = true\nstab_hho = true\n")
+    r = subprocess.run([os.path.join(BIN, "convergence_test"), str(cfg)], capture_output=True, text=True, check=True)
+    rates = re.findall(r"L2 [0-9.e+-]+ \(([0-9.]+)\)\s+energy [0-9.e+-]+ \(([0-9.]+)\)", r.stdout)
+    assert len(rates) == 4
+    # HHO(k+1,k): L2 order k+2, energy order k+1 (convergence_test.cpp:312-325)
+    for (l2, en), k in zip(rates, (1, 1, 2, 2)):
+        assert abs(float(l2) - (k + 2)) < 0.25 and abs(float(en) - (k + 1)) < 0.15
