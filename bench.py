@@ -173,7 +173,7 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(tt); nnz_all, rows_all = int(tt[0]), int(tt[1])
     # SpMV on the implicit block structure: 8 B per value, one 56-byte BlockRow + 8-byte offset per free
     # face, x read + y write per row.  (The scalar-CSR product of SURVEY §8d would move 12*nnz + 20*n.)
-    spmv_bytes = 8.0 * nnz + 64.0 * n_rows / hdi.fbs + 16.0 * n_rows
+    spmv_bytes = (8.0 * nnz + 64.0 * n_rows / hdi.fbs + 16.0 * n_rows) if hdi.fbs > 1 else (12.0 * nnz + 20.0 * n_rows)
     iter_bytes = spmv_bytes + 11 * 8.0 * n_rows                 # + vector passes of the dir / xrz kernels
     r_tol = t_tol = None
     if world == 1 and not args.no_cg_tol:

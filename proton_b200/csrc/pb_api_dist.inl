@@ -101,6 +101,13 @@ static pb_status halo_exchange(pb_ctx* ctx, double* full) {
     return PB_OK;
 }
 
+// resident blocks per SM of the block SpMV instance for face basis size F: its persistent grid must be exactly one wave
+// (a second, partial wave costs a third of the kernel: measured)
+template <int F> static int spmv_blk_blocks_per_sm() {
+    static int cached = 0;
+    if (!cached) { if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cached, pcg_spmv_blk_kernel<8, F, 0>, PCG_THREADS, 0) != cudaSuccess || cached < 1) cached = 4; }
+    return cached;
+}
 static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 ? 8 : len <= 24 ? 8 : 16; }
 
 // conjugated_gradient (solver_cg.hpp:63-144) on the condensed system of this context, or of the row of contexts that
@@ -131,7 +138,15 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     const int c_n = multi ? 1 : nblk;
     const int pre = p->apply_preconditioner ? 1 : 0;
     const int lpr = spmv_lanes(F);
-    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4;      // scalar-CSR product kept for comparison runs
+    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1;   // scalar CSR: comparison runs, and F = 1 where a
+                                                                               // 64-byte face record per row costs more than 7 column indices
+    int nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
+    if (!use_csr) {
+        const int occ = F == 1 ? spmv_blk_blocks_per_sm<1>() : F == 2 ? spmv_blk_blocks_per_sm<2>() : F == 3 ? spmv_blk_blocks_per_sm<3>() : spmv_blk_blocks_per_sm<4>();
+        nblk_sp = nsm * occ; if (nblk_sp > PCG_MAX_BLOCKS) nblk_sp = PCG_MAX_BLOCKS;
+        const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < nblk_sp) nblk_sp = (int)(wantg < 1 ? 1 : wantg);
+    }
+    const int c_ndy = multi ? 1 : nblk_sp;
     cudaStream_t sm = ctx->stream;
     auto reduce_rr_rz = [&]() -> pb_status {
         if (!multi) return PB_OK;
@@ -146,37 +161,56 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
     pcg_init_state_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, ctx->cg);
     CK(cudaGetLastError());
-    CgState hs{}; long long it = 0; const long long check_every = 32;
-    while (true) {
-        for (long long k = 0; k < check_every; k++, it++) {
-            if (it > 0) {
-                pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, ctx->z, ctx->d, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
-                pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, it - 1, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+    // one iteration = [dir, commit] (skipped in the very first one), halo exchange, spmv, xrz (+ all-reduces)
+    auto spmv_xrz = [&]() -> pb_status {
+        { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
+#define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<nblk_sp, PCG_THREADS, 0, sm>>>(n, xoff, ctx->brows, ctx->brp, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg)
+        if (use_csr) {
+            switch (lpr) {
+            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
+            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
             }
-            { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
-#define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->brows, ctx->brp, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg)
-            if (use_csr) {
-                switch (lpr) {
-                case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-                case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-                default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-                }
-            } else {
-                switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
-            }
-#undef PB_SPMV
-            if (multi) {
-                pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk, p_dy, s_dy, nullptr, nullptr);
-                NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
-            }
-            pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, c_n, c_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
-            { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
+        } else {
+            switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
         }
+#undef PB_SPMV
+        if (multi) {
+            pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk_sp, p_dy, s_dy, nullptr, nullptr);
+            NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
+        }
+        pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, c_ndy, c_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
+        return reduce_rr_rz();
+    };
+    auto full_iteration = [&]() -> pb_status {
+        pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, ctx->z, ctx->d, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+        pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+        return spmv_xrz();
+    };
+    CgState hs{}; const int check_every = 32;
+    { pb_status st = spmv_xrz(); if (st != PB_OK) return st; }
+    // the iteration carries no host-side state (the kernels read the iteration number and the exit flag from device
+    // memory), so a batch of `check_every` iterations is captured once into a CUDA graph and replayed; the host only
+    // polls the state between batches.  Multi-rank runs keep plain launches (NCCL calls between the kernels).
+    cudaGraph_t graph = nullptr; cudaGraphExec_t gexec = nullptr;
+    if (!multi && !getenv("PB_PCG_NO_GRAPH")) {
+        CK(cudaStreamBeginCapture(sm, cudaStreamCaptureModeThreadLocal));
+        pb_status cst = PB_OK;
+        for (int k = 0; k < check_every && cst == PB_OK; k++) cst = full_iteration();
+        cudaError_t ce = cudaStreamEndCapture(sm, &graph);
+        if (cst != PB_OK) return cst;
+        CK(ce);
+        CK(cudaGraphInstantiate(&gexec, graph, 0));
+    }
+    while (true) {
+        if (gexec) CK(cudaGraphLaunch(gexec, sm));
+        else for (int k = 0; k < check_every; k++) { pb_status st = full_iteration(); if (st != PB_OK) return st; }
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, sm));
         CK(cudaStreamSynchronize(sm));
         if (hs.done) break;
     }
+    if (gexec) { cudaGraphExecDestroy(gexec); cudaGraphDestroy(graph); }
     CK(cudaEventRecord(ctx->ev[1], sm)); CK(cudaStreamSynchronize(sm));
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
     if (res) {

@@ -92,7 +92,7 @@ __global__ void pcg_init_state_kernel(int nparts, const double* parts_rr, const 
 // y = A d (+ partials of d.y).  LPR lanes cooperate on one row (rows have <= 7*F entries), so a warp reads
 // 32/LPR consecutive rows = one contiguous run of val/col.  xoff: d is stored for columns [xoff, ...).
 template <int LPR>
-__global__ void pcg_spmv_kernel(long long n, long long xoff, const long long* __restrict__ rowptr, const int* __restrict__ col,
+__global__ void __launch_bounds__(PCG_THREADS, 8) pcg_spmv_kernel(long long n, long long xoff, const long long* __restrict__ rowptr, const int* __restrict__ col,
                                 const double* __restrict__ val, const double* __restrict__ dvec, long long down,
                                 double* __restrict__ y, double* __restrict__ parts_dy, const CgState* st) {
     __shared__ double sh[32];
@@ -186,12 +186,14 @@ __global__ void pcg_xrz_kernel(long long n, int precond, int nparts, const doubl
 }
 
 // exit tests in the reference's order (solver_cg.hpp:112-125), then beta = (r.z)/rho, d = z + beta d, iter++.
-// `iter` = number of completed direction updates before this call.
+// st->iters = number of completed direction updates before this call.
 __global__ void pcg_dir_kernel(long long n, int nparts, const double* __restrict__ parts_rr, const double* __restrict__ parts_rz,
-                               const double* __restrict__ z, double* __restrict__ d, long long iter, double tol, double divtol,
+                               const double* __restrict__ z, double* __restrict__ d, double tol, double divtol,
                                long long max_iter, CgState* st) {
     __shared__ double sh[32];
     if (st->done) return;
+    const long long iter = st->iters;       // read before pcg_commit_kernel (the next launch) advances it: the launch
+                                            // sequence carries no host-side iteration number and can be replayed as a graph
     double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
     double rel = sqrt(rr) / st->nr0;
     int reason = -1;
@@ -206,10 +208,11 @@ __global__ void pcg_dir_kernel(long long n, int nparts, const double* __restrict
         d[i] = z[i] + beta * d[i];
 }
 // single-block bookkeeping after pcg_dir_kernel: same decisions, written once
-__global__ void pcg_commit_kernel(int nparts, const double* parts_rr, const double* parts_rz, long long iter, double tol, double divtol,
+__global__ void pcg_commit_kernel(int nparts, const double* parts_rr, const double* parts_rz, double tol, double divtol,
                                   long long max_iter, CgState* st) {
     __shared__ double sh[32];
     if (st->done) return;
+    const long long iter = st->iters;
     double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
     if (threadIdx.x != 0) return;
     double rel = sqrt(rr) / st->nr0;

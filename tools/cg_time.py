@@ -15,7 +15,7 @@ for mode in ("blk", "csr"):
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 20, True))
     r = ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 200, True))
     ms = ctx.timings()["ms_pcg"] / (r["iterations"] + 1)
-    spmv = (12.0 * nnz + 20.0 * n) if mode == "csr" else (8.0 * nnz + 64.0 * n / F + 16.0 * n)
+    spmv = (12.0 * nnz + 20.0 * n) if (mode == "csr" or F == 1) else (8.0 * nnz + 64.0 * n / F + 16.0 * n)
     by = spmv + 11 * 8.0 * n
     print(f"k={k} N={N} spmv={mode}: {ms:.3f} ms/iter, {by/1e9:.2f} GB/iter -> {by/ms/1e6:.0f} GB/s", flush=True)
 t = ctx.timings()
