@@ -31,6 +31,7 @@ struct pb_ctx {
     Grid grid{}; Strip strip{}; int quad_kind = 0;
     long long npoints = 0, ncells_local = 0, ncells_global = 0;
     double2* points = nullptr;
+    StiffEnt* stiff_tab = nullptr; int stiff_key = -1;      // K1: stiff_table of the last reconstruction degree
     // cutHHO user data (whole mesh)
     LevelSet ls{}; bool have_ls = false, have_cut = false;
     int *node_loc = nullptr, *face_loc = nullptr, *cell_loc_g = nullptr, *cut_cells = nullptr;
@@ -156,7 +157,7 @@ static void free_cut(pb_ctx* c) {
 extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     if (!ctx) return PB_OK;
     cudaSetDevice(ctx->device);
-    free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->cg);
+    free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->stiff_tab); dfree(&ctx->cg);
     dist_release(ctx);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -244,9 +245,23 @@ extern "C" pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table) {
 
 // ------------------------------------------------------------------------------------------------ stage 1+2
 template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB>
-static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A) {
+static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A_) {
     constexpr int QC = cell_qps(QK, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
-    using SM = LocalSmem<CD, FD, QCMAX>;
+    using SM = LocalSmem<CD, FD, GS, QCMAX>;
+    LocalArgs A = A_;
+    {   // moment -> stiffness table of this reconstruction degree
+        constexpr int RD = FD + 1, M = cell_basis_size(RD) - 1;
+        if (c->stiff_key != RD * 1000 + SM::MP) {
+            std::vector<StiffEnt> tab((size_t)M * (M + 1) / 2);
+            stiff_table<RD, SM::MP>(tab.data());
+            cudaError_t e0 = dalloc(c, &c->stiff_tab, tab.size());
+            if (e0 == cudaSuccess) e0 = cudaMemcpyAsync(c->stiff_tab, tab.data(), tab.size() * sizeof(StiffEnt), cudaMemcpyHostToDevice, c->stream);
+            if (e0 == cudaSuccess) e0 = cudaStreamSynchronize(c->stream);
+            if (e0 != cudaSuccess) return e0;
+            c->stiff_key = RD * 1000 + SM::MP;
+        }
+        A.stiff = c->stiff_tab;
+    }
     const size_t smem = sizeof(SM) * (TPB / GS);
     auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS, TPB, MINB>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -269,9 +284,9 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
     {   // tuning hook: alternative lane mappings of the headline instance
         const char* e = getenv("PB_K1_GS");
         if (e && cd == 3 && fd == 2 && qk == 0 && sk == 1 && rqd == 6) {
-            if (atoi(e) == 16) return launch_local<3, 2, 0, 1, 6, 16, 32, 16>(c, A);
-            if (atoi(e) == 1612) return launch_local<3, 2, 0, 1, 6, 16, 32, 12>(c, A);
-            if (atoi(e) == 806) return launch_local<3, 2, 0, 1, 6, 8, 32, 6>(c, A);
+            if (atoi(e) == 8256) return launch_local<3, 2, 0, 1, 6, 8, 256, 1>(c, A);
+            if (atoi(e) == 8128) return launch_local<3, 2, 0, 1, 6, 8, 128, 2>(c, A);
+            if (atoi(e) == 864) return launch_local<3, 2, 0, 1, 6, 8, 64, 4>(c, A);
         }
     }
 #ifdef PB_FAST_BUILD   // developer builds: only the headline instance
