@@ -249,6 +249,7 @@ static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A_) {
     constexpr int QC = cell_qps(QK, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
     using SM = LocalSmem<CD, FD, GS, QCMAX>;
     LocalArgs A = A_;
+    if (A.ncells >= (1ll << 31)) return cudaErrorInvalidValue;      // K1 indexes local cells with 32 bits
     {   // moment -> stiffness table of this reconstruction degree
         constexpr int RD = FD + 1, M = cell_basis_size(RD) - 1;
         if (c->stiff_key != RD * 1000 + SM::MP) {
@@ -284,9 +285,8 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
     {   // tuning hook: alternative lane mappings of the headline instance
         const char* e = getenv("PB_K1_GS");
         if (e && cd == 3 && fd == 2 && qk == 0 && sk == 1 && rqd == 6) {
-            if (atoi(e) == 8256) return launch_local<3, 2, 0, 1, 6, 8, 256, 1>(c, A);
-            if (atoi(e) == 8128) return launch_local<3, 2, 0, 1, 6, 8, 128, 2>(c, A);
-            if (atoi(e) == 864) return launch_local<3, 2, 0, 1, 6, 8, 64, 4>(c, A);
+            if (atoi(e) == 1612) return launch_local<3, 2, 0, 1, 6, 16, 32, 12>(c, A);
+            if (atoi(e) == 1610) return launch_local<3, 2, 0, 1, 6, 16, 32, 10>(c, A);
         }
     }
 #ifdef PB_FAST_BUILD   // developer builds: only the headline instance

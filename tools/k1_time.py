@@ -8,7 +8,7 @@ k = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 ctx = pb.Context(0)
 ctx.mesh(pb.mesh_init_params(N, N))
 hdi = pb.hho_degree_info(k + 1, k)
-for gs in [""]:
+for gs in ([""] + os.environ.get("K1_VARIANTS", "").split()):
     if gs: os.environ["PB_K1_GS"] = gs
     else: os.environ.pop("PB_K1_GS", None)
     ts = []

@@ -90,4 +90,8 @@ if src and ph:
         f64 = sum(1 for a, (c, o, t) in addr_line.items() if o is not None and lo <= o <= hi and t.split()[0].split(".")[0] in ("DFMA", "DMUL", "DADD") or
                   (o is not None and lo <= o <= hi and t.startswith("@") and len(t.split()) > 1 and t.split()[1].split(".")[0] in ("DFMA", "DMUL", "DADD")))
         wf = sum(v for k, v in wf_outer.items() if k is not None and lo <= k <= hi)
-        print(f"{name:16s} {st:6d} {100 * dy / tot_d:6.2f} {100 * sa / tot_s:7.2f} {f64:8d} {100 * wf / tot_w:10.2f}")
+        stc = collections.Counter()
+        for k_, v_ in stall.items():
+            if k_ is not None and lo <= k_ <= hi: stc.update(v_)
+        top = ", ".join(f"{n_[6:]}:{100 * v_ / max(sa, 1):.0f}%" for n_, v_ in stc.most_common(4))
+        print(f"{name:16s} {st:6d} {100 * dy / tot_d:6.2f} {100 * sa / tot_s:7.2f} {f64:8d} {100 * wf / tot_w:10.2f}   {top}")
