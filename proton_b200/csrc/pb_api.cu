@@ -263,7 +263,7 @@ static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A_) {
         }
         A.stiff = c->stiff_tab;
     }
-    const size_t smem = sizeof(SM) * (TPB / GS);
+    const size_t smem = local_ref_bytes<CD, FD, QK, RQD>() + sizeof(SM) * (TPB / GS);
     auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS, TPB, MINB>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
