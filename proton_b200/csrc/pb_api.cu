@@ -285,8 +285,8 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
     {   // tuning hook: alternative lane mappings of the headline instance
         const char* e = getenv("PB_K1_GS");
         if (e && cd == 3 && fd == 2 && qk == 0 && sk == 1 && rqd == 6) {
-            if (atoi(e) == 1612) return launch_local<3, 2, 0, 1, 6, 16, 32, 12>(c, A);
-            if (atoi(e) == 1610) return launch_local<3, 2, 0, 1, 6, 16, 32, 10>(c, A);
+            if (atoi(e) == 8256) return launch_local<3, 2, 0, 1, 6, 8, 256, 1>(c, A);
+            if (atoi(e) == 8128) return launch_local<3, 2, 0, 1, 6, 8, 128, 2>(c, A);
         }
     }
 #ifdef PB_FAST_BUILD   // developer builds: only the headline instance
