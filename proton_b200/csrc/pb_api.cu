@@ -360,9 +360,14 @@ static pb_status launch_generic(pb_ctx* ctx, const LocalArgs& A, int cd, int fd,
 // K3: condensed blocks -> CSR values and rhs
 static pb_status scatter_system(pb_ctx* ctx) {
     const int F = ctx->F;
-    scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
-    CK(cudaGetLastError());
-    scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
+#define PB_SC(F_) scatter_kernel_t<F_, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs)
+    if (F == 1) PB_SC(1); else if (F == 2) PB_SC(2); else if (F == 3) PB_SC(3); else if (F == 4) PB_SC(4);
+    else {      // face degree > 3 (generic local kernel)
+        scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
+        CK(cudaGetLastError());
+        scatter_rhs_kernel<<<(unsigned)((ctx->nrows + 255) / 256), 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->g, ctx->rhs);
+    }
+#undef PB_SC
     CK(cudaGetLastError());
     return PB_OK;
 }
