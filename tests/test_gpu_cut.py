@@ -121,3 +121,31 @@ def test_cut_k3_is_refused(ctx):
     gpu_cut_mesh(ctx, 10, 4)
     with pytest.raises(pb.ProtonError, match="k <= 2|no kernel instance"):
         ctx.assemble(pb.hho_degree_info(4, 3), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+
+
+@pytest.mark.parametrize("k,N,cuts", [(1, 12, (0, 5, 12)), (2, 10, (0, 3, 6, 10))])
+def test_cut_strip_contexts_assemble_the_same_rows(k, N, cuts):
+    """multi-GPU partition of the fictitious-domain problem: every strip context preprocesses the whole level set,
+    assembles its rows (uncut cells by K1, cut cells by K2, ghost row included) and reproduces the whole-mesh CSR rows
+    bit for bit."""
+    hdi = pb.hho_degree_info(k + 1, k)
+    whole = pb.Context(0)
+    gpu_cut_mesh(whole, N, 4)
+    whole.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+    rp, col, val, rhs = whole.csr()
+    for rb, re in zip(cuts[:-1], cuts[1:]):
+        c = pb.Context(0)
+        c.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT, row_begin=rb, row_end=re)
+        c.cut_levelset(0, 0.35, 0.5, 0.5)
+        c.cut_preprocess(4)
+        c.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+        L = pb.strip_layout(N, N, rb, re, hdi.fbs)
+        rp_s, col_s, val_s, rhs_s = c.csr()
+        r0 = L["cf_begin"] * hdi.fbs
+        lo, hi = rp[r0], rp[r0 + c.n_rows]
+        assert np.array_equal(rp_s, rp[r0 : r0 + c.n_rows + 1] - lo)
+        assert np.array_equal(col_s, col[lo:hi])
+        assert np.array_equal(val_s, val[lo:hi])
+        assert np.array_equal(rhs_s, rhs[r0 : r0 + c.n_rows])
+        c.close()
+    whole.close()
