@@ -103,6 +103,49 @@ def run_reference(args, rank, world):
     print(json.dumps(out), flush=True)
 
 
+def cut_record(args, rank, world, dev, dist, torch, pb, PB):
+    """Secondary record (not the headline): BASELINE's target, cutHHO fictitious-domain Poisson k=2, circle level set, on
+    cut_N x cut_N quads sharded by cell rows over the ranks (fixed total size).  Preprocessing on the device, assembly
+    (K1 Dunavant-fan uncut cells + K2 cut cells + K3), a fixed number of PCG iterations for the bandwidth figure."""
+    from proton_b200.dist import make_rank_context
+    Nc, k = args.cut_N, 2
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx = make_rank_context(pb.mesh_init_params(Nc, Nc), PB.QUAD_POLY_DUNAVANT, rank, world, dev, dist)
+
+    def sync_all():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+    sync_all(); t0 = time.perf_counter()
+    ctx.cut_levelset(0, 1.0 / 3.0, 0.5, 0.5)
+    ctx.cut_preprocess(4)
+    sync_all(); prep_ms = (time.perf_counter() - t0) * 1e3
+    for _ in range(2):
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+    sync_all()
+    ms = []
+    for _ in range(3):
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+        t = ctx.timings(); ms.append(t["ms_local"] + t["ms_scatter"])
+    asm_ms = sum(ms) / len(ms)
+    ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 20, True))
+    sync_all()
+    ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 100, True))
+    it_ms = ctx.timings()["ms_pcg"] / 101.0
+    vals = [asm_ms, it_ms, prep_ms]
+    nnz, rows, ncut = ctx.nnz, ctx.n_rows, ctx.cut_counts()[0]
+    if dist is not None:
+        tt = torch.tensor(vals, dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); vals = [float(v) for v in tt.tolist()]
+        tt = torch.tensor([nnz, rows], dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt); nnz, rows = int(tt[0]), int(tt[1])
+    ctx.close()
+    hbm, _ = peaks()
+    iter_bytes = (8.0 * nnz + 64.0 * rows / hdi.fbs + 16.0 * rows + 11 * 8.0 * rows) / world
+    return {"workload": f"cutHHO fictitious-domain Poisson k=2, circle level set r=1/3, {Nc}x{Nc} quads sharded over {world} GPU(s) by cell rows (BASELINE target; "
+                        "k=3 of config 4 has no valid reference answer, SURVEY F4)",
+            "preprocess_ms": vals[2], "assemble_ms": vals[0], "cells_per_s": Nc * Nc / (vals[0] * 1e-3), "cut_cells": ncut,
+            "pcg_ms_per_iter": vals[1], "pcg_hbm_frac": iter_bytes / (vals[1] * 1e-3) / 1e9 / hbm, "unknowns": rows, "nnz": nnz}
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -218,7 +261,10 @@ def run_ours(args, rank, world, local_rank):
                         "flop_per_cell": flop, "flop_model": "reference-algorithm flops (SURVEY 8d), not executed flops", "ms_per_launch": k1, "traffic": None},
            "e2e": {"value": cells_total / (e2e_ms * 1e-3), "unit": "cells/s", "h2d_bytes_per_step": int(ctx.npoints * 16), "d2h_bytes_per_step": int(n_rows * 8),
                    "ms_per_step": e2e_ms, "rhs_checksum": checksum},
-           "gpu_launches": 3 * args.steps, "cg": cg}
+           "gpu_launches": 2 * args.steps, "cg": cg}
+    ctx.close()
+    if not args.no_cut:
+        out["target_cut"] = cut_record(args, rank, world, dev, dist, torch, pb, PB)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
@@ -227,7 +273,6 @@ def run_ours(args, rank, world, local_rank):
             out["cpu_baseline"] = {"value": m.ncells / dt, "unit": "cells/s", "cores": 1, "kind": "port",
                                    "sample": f"same workload on {args.cpu_N}x{args.cpu_N} cells, oracle/ restatement of the reference's serial assembly loop (-O3 -mavx), {dt:.1f} s"}
         print(json.dumps(out), flush=True)
-    ctx.close()
     if dist is not None:
         dist.destroy_process_group()
 
@@ -244,6 +289,8 @@ def main():
     ap.add_argument("--cpu-N", dest="cpu_N", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cg-tol", action="store_true", help="skip the solve-to-tolerance run (fixed-iteration bandwidth run only)")
+    ap.add_argument("--no-cut", action="store_true", help="skip the secondary cutHHO record")
+    ap.add_argument("--cut-N", dest="cut_N", type=int, default=4096)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))

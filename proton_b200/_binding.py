@@ -204,6 +204,12 @@ class Context:
         self._ck(lib().pb_cut_download(self._h, None, None, None, None, None, None, _ptr(pts)))
         return dict(node_loc=nl, face_loc=fl, face_ip=fip, cell_loc=cl, iface_pts=pts)
 
+    def cut_counts(self):
+        """(number of cut cells, interface points per cut cell) of the last preprocessing"""
+        ncut = C.c_longlong(); ni = C.c_int()
+        self._ck(lib().pb_cut_download(self._h, None, None, None, None, C.byref(ncut), C.byref(ni), None))
+        return ncut.value, ni.value
+
     # ---- stages 1+2
     def assemble(self, hdi, stab_kind=PB.STAB_FANCY, problem=PB.PROBLEM_HHO, fun=PB.FUN_SINSIN, rhs_degree_increase=0, eta=5.0, keep_local=False):
         p = _AssemblyParams(hdi.cd, hdi.fd, stab_kind, problem, fun, rhs_degree_increase, eta, int(keep_local))

@@ -40,6 +40,29 @@ def main():
             ok = ok and err < 1e-9 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2
             ref.close()
         ctx.close()
+    # fictitious-domain problem (cut cells by K2): every rank preprocesses the whole level set, assembles its strip
+    for (N, k) in [(20, 1), (24, 2)]:
+        mip = pb.mesh_init_params(N, N)
+        hdi = pb.hho_degree_info(k + 1, k)
+        ctx = make_rank_context(mip, PB.QUAD_POLY_DUNAVANT, rank, world, lr, dist)
+        ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+        res = ctx.conjugated_gradient(pb.cg_params(1e-14, 100.0, 100000, True))
+        cells, faces = ctx.recover_strip(ctx.row_begin, ctx.row_end)
+        gc = [None] * world; gf = [None] * world
+        dist.all_gather_object(gc, cells); dist.all_gather_object(gf, faces)
+        if rank == 0:
+            ref = pb.Context(lr)
+            ref.mesh(mip, PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
+            ref.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+            r1 = ref.conjugated_gradient(pb.cg_params(1e-14, 100.0, 100000, True))
+            full = ref.recover()
+            got = np.concatenate(gc + gf)
+            err = np.linalg.norm(got - full) / np.linalg.norm(full)
+            print(f"fictdom N={N} k={k} world={world}: iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, rel diff {err:.2e}", flush=True)
+            ok = ok and err < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED
+            ref.close()
+        ctx.close()
     flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()
