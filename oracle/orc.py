@@ -34,7 +34,7 @@ def lib():
         build()
         L = C.CDLL(_SO)
         L.orc_last_error.restype = C.c_char_p
-        for f in ("orc_mesh_new", "orc_assemble", "orc_obstacle_assemble"):
+        for f in ("orc_mesh_new", "orc_assemble", "orc_assemble_mt", "orc_obstacle_assemble"):
             getattr(L, f).restype = C.c_void_p
         L.orc_mesh_new.argtypes = [C.c_longlong, C.c_longlong, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int]
         L.orc_cell_quadrature.restype = C.c_longlong
@@ -122,17 +122,25 @@ class Mesh:
         lib().orc_cell_quadrature(self.h, C.c_longlong(cell), degree, kind, int(where_aware), _p(pts), _p(w))
         return pts, w
 
-    def assemble(self, cd, fd, stab=STAB_FANCY, problem=0, fun=FUN_SINSIN, rhs_di=0):
-        return System(self, cd, fd, stab, problem, fun, rhs_di)
+    @staticmethod
+    def omp_enabled():
+        return bool(lib().orc_omp_enabled())
+
+    def assemble(self, cd, fd, stab=STAB_FANCY, problem=0, fun=FUN_SINSIN, rhs_di=0, threads=1):
+        """threads > 1: local operators by that many OpenMP threads over the cells (the reference loop is serial)"""
+        return System(self, cd, fd, stab, problem, fun, rhs_di, threads)
 
 
 class System:
     """Full (uncondensed) cell+face system of the reference assembler (hho.hpp:252-463)."""
 
-    def __init__(self, mesh, cd, fd, stab, problem, fun, rhs_di):
+    def __init__(self, mesh, cd, fd, stab, problem, fun, rhs_di, threads=1):
         self.mesh = mesh
         tl = C.c_double(0); tg = C.c_double(0)
-        h = lib().orc_assemble(mesh.h, cd, fd, stab, problem, fun, rhs_di, C.byref(tl), C.byref(tg))
+        if threads > 1:
+            h = lib().orc_assemble_mt(mesh.h, cd, fd, stab, problem, fun, rhs_di, int(threads), C.byref(tl), C.byref(tg))
+        else:
+            h = lib().orc_assemble(mesh.h, cd, fd, stab, problem, fun, rhs_di, C.byref(tl), C.byref(tg))
         if not h:
             raise RuntimeError(lib().orc_last_error().decode())
         self.h = C.c_void_p(h)

@@ -162,6 +162,38 @@ void* orc_assemble(void* h, int cd, int fd, int stab_kind, int problem, int fun,
     return S;
     ORC_CATCH(nullptr)
 }
+/* The same loop with the local operators computed by `nthreads` OpenMP threads over the cells (the reference is serial; this
+   is the "all host threads" variant of the CPU baseline): assembler.assemble and finalize stay serial and in cell order, so the
+   system is identical to orc_assemble's. */
+void* orc_assemble_mt(void* h, int cd, int fd, int stab_kind, int problem, int fun, int rhs_di, int nthreads, double* seconds_local, double* seconds_global) {
+    ORC_TRY
+    auto* H = (MeshH*)h; Problem P(cd, fd); P.stab = stab_kind; P.problem = problem; P.fun = fun; P.rhs_di = rhs_di;
+    auto* S = new SysH(H, P);
+    Fun bc = sol_fun(fun);
+    const long long nc = (long long)H->m.cells.size();
+    std::vector<Mat> lcs(nc); std::vector<Vec> rs(nc);
+    auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (long long c = 0; c < nc; c++) {
+        Mat o, d, s; local_ops(*H, H->m.cells[c], P, o, d, s, rs[c]);
+        lcs[c] = d + s;
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    for (long long c = 0; c < nc; c++) S->as.assemble(H->m, H->m.cells[c], lcs[c], rs[c], bc);
+    S->as.finalize();
+    auto t2 = std::chrono::steady_clock::now();
+    if (seconds_local) *seconds_local = std::chrono::duration<double>(t1 - t0).count();
+    if (seconds_global) *seconds_global = std::chrono::duration<double>(t2 - t1).count();
+    return S;
+    ORC_CATCH(nullptr)
+}
+int orc_omp_enabled() {
+#ifdef _OPENMP
+    return 1;
+#else
+    return 0;
+#endif
+}
 void orc_sys_free(void* s) { delete (SysH*)s; }
 void orc_sys_sizes(void* s, long long out[2]) { auto* S = (SysH*)s; out[0] = S->as.LHS.n; out[1] = S->as.LHS.val.size(); }
 void orc_sys_get(void* s, long long* rowptr, int* col, double* val, double* rhs, long long* compress) {
