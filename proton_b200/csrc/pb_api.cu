@@ -282,24 +282,35 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
     *found = true;
 #define PB_CASE(CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_) \
     if (cd == CD_ && fd == FD_ && qk == QK_ && sk == SK_ && rqd == RQD_) return launch_local<CD_, FD_, QK_, SK_, RQD_, GS_, TPB_, MINB_>(c, A);
-    {   // tuning hook: alternative lane mappings of the headline instance
+    {   // tuning hook: alternative lane mappings (developer experiments, PB_K1_GS=<id>)
         const char* e = getenv("PB_K1_GS");
-        if (e && cd == 3 && fd == 2 && qk == 0 && sk == 1 && rqd == 6) {
-            if (atoi(e) == 8256) return launch_local<3, 2, 0, 1, 6, 8, 256, 1>(c, A);
-            if (atoi(e) == 8128) return launch_local<3, 2, 0, 1, 6, 8, 128, 2>(c, A);
+        const int v = e ? atoi(e) : 0;
+        if (v && qk == 0 && sk == 1) {
+#ifndef PB_FAST_BUILD
+            if (cd == 2 && fd == 1 && rqd == 4) {
+                if (v == 1) return launch_local<2, 1, 0, 1, 4, 4, 32, 10>(c, A);
+                if (v == 2) return launch_local<2, 1, 0, 1, 4, 4, 64, 6>(c, A);
+                if (v == 3) return launch_local<2, 1, 0, 1, 4, 4, 32, 14>(c, A);
+            }
+            if (cd == 1 && fd == 0 && rqd == 2) {
+                if (v == 1) return launch_local<1, 0, 0, 1, 2, 2, 32, 16>(c, A);
+                if (v == 2) return launch_local<1, 0, 0, 1, 2, 2, 64, 8>(c, A);
+                if (v == 3) return launch_local<1, 0, 0, 1, 2, 4, 32, 24>(c, A);
+            }
+#endif
         }
     }
 #ifdef PB_FAST_BUILD   // developer builds: only the headline instance
     PB_CASE(3, 2, 0, 1, 6, 8, 32, 8)
 #else
     // HHO(k+1,k), tensor Gauss (convergence_test): fancy and naive
-    PB_CASE(1, 0, 0, 1, 2, 8, 64, 8)  PB_CASE(1, 0, 0, 0, 2, 8, 64, 8)
-    PB_CASE(2, 1, 0, 1, 4, 8, 32, 12) PB_CASE(2, 1, 0, 0, 4, 8, 32, 12)
+    PB_CASE(1, 0, 0, 1, 2, 4, 32, 16)  PB_CASE(1, 0, 0, 0, 2, 4, 32, 16)
+    PB_CASE(2, 1, 0, 1, 4, 4, 32, 12) PB_CASE(2, 1, 0, 0, 4, 4, 32, 12)
     PB_CASE(3, 2, 0, 1, 6, 8, 32, 8) PB_CASE(3, 2, 0, 0, 6, 8, 32, 8)
     PB_CASE(4, 3, 0, 1, 8, 16, 32, 5) PB_CASE(4, 3, 0, 0, 8, 16, 32, 5)
     // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive
-    PB_CASE(1, 0, 1, 0, 2, 8, 64, 8)
-    PB_CASE(2, 1, 1, 0, 4, 8, 32, 12)
+    PB_CASE(1, 0, 1, 0, 2, 4, 32, 16)
+    PB_CASE(2, 1, 1, 0, 4, 4, 32, 12)
     PB_CASE(3, 2, 1, 0, 6, 8, 32, 8)
 #endif
 #undef PB_CASE
