@@ -372,7 +372,9 @@ static pb_status launch_generic(pb_ctx* ctx, const LocalArgs& A, int cd, int fd,
 static pb_status scatter_system(pb_ctx* ctx) {
     const int F = ctx->F;
 #define PB_SC(F_) scatter_kernel_t<F_, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs)
-    if (F == 1) PB_SC(1); else if (F == 2) PB_SC(2); else if (F == 3) PB_SC(3); else if (F == 4) PB_SC(4);
+    if (F == 1) scatter_packed_kernel_t<1, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
+    else if (F == 2) scatter_packed_kernel_t<2, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
+    else if (F == 3) PB_SC(3); else if (F == 4) PB_SC(4);
     else {      // face degree > 3 (generic local kernel)
         scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);
         CK(cudaGetLastError());

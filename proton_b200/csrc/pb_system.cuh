@@ -169,6 +169,69 @@ __global__ void __launch_bounds__(256) scatter_kernel_t(long long nrows_blk, con
     }
 }
 
+// the same for small face degrees (F = 1, 2): a scalar row has only 7F <= 14 entries, so 28/(7F) block rows sit side by side
+// in one warp, lane = (row slot, position (b, bc) inside the scalar row).  (For F >= 3 this variant measured slower
+// than the one-row kernel above: 3.5 vs 2.6 ms at k = 2.)  The lane's source offsets are fixed per block row,
+// so the inner loop is two loads, one add, one store.  U block rows per warp pass; measured on B200 at k = 2, 2048^2:
+// U = 1 with >= 32 blocks per SM is fastest (2.55 ms, 4.2 TB/s); U > 1 strides the rows of a warp apart and loses the
+// L2 reuse of the S blocks between the four faces of a cell.  Lanes 28.. write the rhs rows.
+template <int F, int U>
+__global__ void __launch_bounds__(256) scatter_packed_kernel_t(long long nrows_blk, const BlockRow* __restrict__ rows, const long long* __restrict__ brp,
+                                                        const double* __restrict__ S, const double* __restrict__ g,
+                                                        double* __restrict__ val, double* __restrict__ rhs) {
+    static_assert(7 * F <= 28, "lanes 28..31 carry the rhs");
+    constexpr int NF = 4 * F, W = 7 * F, RPW = 28 / W;          // RPW block rows side by side in one warp (4 / 2 / 1 / 1 for F = 1..4)
+    const int lane = threadIdx.x & 31;
+    const int slot = lane < 28 ? lane / W : 0, pos = lane - slot * W;          // lanes < 28: (block row slot, position in the scalar row)
+    const int b = pos / F, bc = pos - b * F;
+    const int rs = lane >= 28 ? (lane - 28) / F : 0, ra = lane >= 28 ? (lane - 28) - rs * F : 0;      // lanes >= 28: (slot, scalar row) of a rhs entry
+    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long br0 = ((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5) * RPW; br0 < nrows_blk; br0 += U * nwarps * RPW) {
+        double v[U][F];
+        double* out[U]; int rowlen[U]; bool on[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const long long br = br0 + u * nwarps * RPW + (lane < 28 ? slot : rs);
+            on[u] = false; rowlen[u] = 0; out[u] = nullptr;
+#pragma unroll
+            for (int a = 0; a < F; a++) v[u][a] = 0.0;
+            if (br < nrows_blk) {
+                const BlockRow& R = rows[br];
+                if (lane < 28) {
+                    rowlen[u] = R.nb * F;
+                    if (slot < RPW && pos < rowlen[u]) {
+                        on[u] = true;
+                        out[u] = val + brp[br] * (F * F) + pos;
+                        const double* S0 = S + (long long)R.cell[0] * (NF * NF) + R.li[0] * F * NF;
+                        const double* S1 = S + (long long)R.cell[1] * (NF * NF) + R.li[1] * F * NF;
+                        const int l0 = R.src[0][b], l1 = R.src[1][b];
+                        // S is symmetric up to rounding: read the transposed entry so that bc runs over contiguous doubles
+#pragma unroll
+                        for (int a = 0; a < F; a++) {
+                            double v0 = 0.0, v1 = 0.0;
+                            if (l0 != 255) v0 = S0[a * NF + l0 * F + bc];
+                            if (l1 != 255) v1 = S1[a * NF + l1 * F + bc];
+                            v[u][a] = v0 + v1;
+                        }
+                    }
+                } else if (lane - 28 < RPW * F) {
+                    v[u][0] = g[(long long)R.cell[0] * NF + R.li[0] * F + ra] + g[(long long)R.cell[1] * NF + R.li[1] * F + ra];
+                    rowlen[u] = -1;          // marks a live rhs lane
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (on[u]) {
+#pragma unroll
+                for (int a = 0; a < F; a++) out[u][a * rowlen[u]] = v[u][a];
+            } else if (rowlen[u] == -1) {
+                rhs[(br0 + u * nwarps * RPW + rs) * F + ra] = v[u][0];
+            }
+        }
+    }
+}
+
 // rhs: one thread per scalar row; g is [cell][NF] (already Dirichlet-lifted)
 __global__ void scatter_rhs_kernel(long long nrows_blk, int F, const BlockRow* rows, const double* __restrict__ g, double* __restrict__ rhs) {
     long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
