@@ -48,6 +48,9 @@ int main(int argc, char** argv) {
                 assembler.assemble_all(ctp.stab_hho ? PB_STAB_FANCY : PB_STAB_NAIVE, PB_PROBLEM_HHO, PB_FUN_SINSIN);
                 pb::cg_params<double> cgp; cgp.apply_preconditioner = ctp.preconditioner; cgp.convergence_threshold = 1e-12;
                 cgp.max_iter = 3 * assembler.system_size();
+                // the reference keeps its default guard (stop when the residual grows 100x); on the condensed face system the
+                // 2-norm residual of Jacobi-PCG overshoots in the first iterations (x160 at k=3, N=512), so the guard is widened
+                cgp.divergence_threshold = 1e8;
                 std::vector<double> sol; size_t iters = 0;
                 if (pb::conjugated_gradient(assembler, sol, cgp, &iters) != pb::cg_exit_reason::CONVERGED) std::cout << "Warning! Solver didn't converge..." << std::endl;
                 auto e = assembler.error_norms();
