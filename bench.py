@@ -71,6 +71,18 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_traffic(kernel, N, k):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json), or None when
+    the capture was taken on another workload."""
+    try:
+        t = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))
+        if t["workload"] != {"N": N, "k": k}:
+            return None
+        return {"bytes": t[kernel]["bytes"], "source": t[kernel]["source"]}
+    except Exception:
+        return None
+
+
 def run_reference(args, rank, world):
     """The reference's own CPU path for stages 1+2 (per-cell operators + assembler.assemble + finalize), timed on the
     host cores.  The reference cannot be built here or on the box (Eigen3/SILO/Lua absent), so this is the plain-C++
@@ -219,7 +231,25 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.steps):
         e2e_step()
     sync_all()
+    e2e_serial_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    serial_checksum = float(rhs_host.sum())
+    # the same steps through pb_assemble_pipelined: step i's read-back and step i+1's upload run on copy streams beside
+    # the kernels (every step still uploads its own vertices and reads its own rhs back, all inside the timed region)
+    rhs_host2 = torch.empty(n_rows, dtype=torch.float64).pin_memory()
+    bufs = [rhs_host, rhs_host2]
+    for i in range(max(2, args.warmup // 2)):
+        ctx.assemble_pipelined(hdi, pts_host.data_ptr(), bufs[i % 2].data_ptr())
+    ctx.pipeline_sync()
+    rhs_host.zero_(); rhs_host2.zero_()
+    sync_all()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ctx.assemble_pipelined(hdi, pts_host.data_ptr(), bufs[i % 2].data_ptr())
+    ctx.pipeline_sync()
+    sync_all()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    rhs_host = bufs[(args.steps - 1) % 2]
+    assert abs(float(rhs_host.sum()) - serial_checksum) <= 1e-12 * abs(serial_checksum), "pipelined step differs from the serial one"
     checksum = float(rhs_host.sum())
 
     # ---------------- stage 3: PCG on the condensed system (all ranks together: NCCL halo exchange + all-reduces)
@@ -250,15 +280,16 @@ def run_ours(args, rank, world, local_rank):
     gbs = iter_bytes / (ms_it * 1e-3) / 1e9                                          # per GPU
     cg = {"unknowns": rows_all, "nnz": nnz_all, "fixed_iterations": its, "ms_per_iter": ms_it, "iter_bytes_per_gpu": iter_bytes,
           "halo_doubles_per_neighbour": (2 * Nx - 1) * hdi.fbs, "allreduces_per_iter": 2 if world > 1 else 0,
-          "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU", "frac": gbs / hbm, "peak_source": hbm_src, "traffic": None}}
+          "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU", "frac": gbs / hbm, "peak_source": hbm_src,
+                       "traffic": (ncu_traffic("pcg_spmv_blk_kernel", N, k) or {}).get("bytes"), "traffic_note": "SpMV kernel alone (algorithmic %.3g B), single-GPU capture" % spmv_bytes}}
     if r_tol is not None:
         cg.update({"tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": t_tol})
 
     # ---------------- reduce over ranks (max time), print on rank 0
     if dist is not None:
-        tt = torch.tensor([ms_step, k1, e2e_ms, wall_ms], dtype=torch.float64, device=f"cuda:{dev}")
+        tt = torch.tensor([ms_step, k1, e2e_ms, wall_ms, e2e_serial_ms], dtype=torch.float64, device=f"cuda:{dev}")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_step, k1, e2e_ms, wall_ms = [float(v) for v in tt.tolist()]
+        ms_step, k1, e2e_ms, wall_ms, e2e_serial_ms = [float(v) for v in tt.tolist()]
     cells_total = cells_rank * world
     value = cells_total / (ms_step * 1e-3)
     flop = FLOP_PER_CELL[k]
@@ -272,9 +303,14 @@ def run_ours(args, rank, world, local_rank):
            "clocks": clk.summary(),
            "roofline": {"bound": "fp64", "kernel": "local_uncut_kernel (K1)", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp64_peak,
                         "peak_source": "measured on this GPU by pb_probe_fp64_peak (register-resident DFMA chains); MEASURED_PEAKS.json has no fp64 entry",
-                        "flop_per_cell": flop, "flop_model": "reference-algorithm flops (SURVEY 8d), not executed flops", "ms_per_launch": k1, "traffic": None},
+                        "flop_per_cell": flop, "flop_model": "reference-algorithm flops (SURVEY 8d), not executed flops", "ms_per_launch": k1,
+                        "traffic": (ncu_traffic("local_uncut_kernel", N, k) or {}).get("bytes"),
+                        "algorithmic_bytes": int(k1_cells * (64 + 8 * (hdi.fbs * 4) * (hdi.fbs * 4 + 1 + hdi.cbs) + 8 * hdi.cbs)),
+                        "traffic_source": (ncu_traffic("local_uncut_kernel", N, k) or {}).get("source")},
            "e2e": {"value": cells_total / (e2e_ms * 1e-3), "unit": "cells/s", "h2d_bytes_per_step": int(ctx.npoints * 16), "d2h_bytes_per_step": int(n_rows * 8),
-                   "ms_per_step": e2e_ms, "rhs_checksum": checksum},
+                   "ms_per_step": e2e_ms, "rhs_checksum": checksum,
+                   "how": "pb_assemble_pipelined: per step, vertices host->device and condensed rhs device->host on copy streams overlapping the kernels of the neighbouring steps",
+                   "serial_ms_per_step": e2e_serial_ms, "serial_value": cells_total / (e2e_serial_ms * 1e-3)},
            "gpu_launches": 2 * args.steps, "cg": cg}
     ctx.close()
     if not args.no_cut:

@@ -96,6 +96,15 @@ pb_status pb_cut_download(pb_ctx* ctx, int* node_location, int* face_location, d
  * static condensation) and assembler.assemble()/finalize() (hho.hpp:344-406, 451-455) onto the condensed face
  * system: row/column of face dof (f,a) = compress_table[f]*fbs + a. ---- */
 pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* params);
+/* The same step for a caller that streams meshes through the device (the driver loop of convergence_test.cpp:186-199
+ * repeated over a mesh sequence; no counterpart in the serial reference).  Returns after enqueueing:
+ *   host_points (page-locked, 2*num_points doubles, may be NULL) is uploaded on a copy stream as soon as the previous
+ *   step's local-operator kernel has released the vertex array;
+ *   host_rhs (page-locked, n_rows doubles, may be NULL) receives assembler.RHS on a second copy stream after the scatter;
+ *   the next step's scatter waits for that read-back.  The caller must not reuse host_rhs before pb_pipeline_sync or
+ *   two further steps, and calls pb_pipeline_sync before reading results (the other entry points do it themselves). */
+pb_status pb_assemble_pipelined(pb_ctx* ctx, const pb_assembly_params* params, const double* host_points, double* host_rhs);
+pb_status pb_pipeline_sync(pb_ctx* ctx);
 pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long long* n_cells, long long* n_local);
 /* assembler.LHS / assembler.RHS of the condensed system, CSR with sorted columns */
 pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs);

@@ -66,6 +66,8 @@ def lib():
         L.pb_mesh_cartesian.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int,
                                         C.c_longlong, C.c_longlong]
         L.pb_get_local.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
+        L.pb_assemble_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pb_pipeline_sync.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -218,6 +220,19 @@ class Context:
         n = C.c_longlong(); nnz = C.c_longlong(); nc = C.c_longlong(); nl = C.c_longlong()
         self._ck(lib().pb_system_sizes(self._h, C.byref(n), C.byref(nnz), C.byref(nc), C.byref(nl)))
         self.n_rows, self.nnz, self.ncells_local, self.n_local = n.value, nnz.value, nc.value, nl.value
+        return self
+
+    def assemble_pipelined(self, hdi, host_points_ptr=None, host_rhs_ptr=None, stab_kind=PB.STAB_FANCY, problem=PB.PROBLEM_HHO, fun=PB.FUN_SINSIN,
+                           rhs_degree_increase=0, eta=5.0):
+        """pb_assemble_pipelined: enqueue one step (upload of the vertices, stages 1+2, read-back of the rhs); page-locked
+        host pointers as integers.  Call pipeline_sync() before using the results."""
+        p = _AssemblyParams(hdi.cd, hdi.fd, stab_kind, problem, fun, rhs_degree_increase, eta, 0)
+        self._ck(lib().pb_assemble_pipelined(self._h, C.byref(p), C.c_void_p(host_points_ptr), C.c_void_p(host_rhs_ptr)))
+        self.hdi = hdi
+        return self
+
+    def pipeline_sync(self):
+        self._ck(lib().pb_pipeline_sync(self._h))
         return self
 
     def csr(self, values=True):

@@ -57,6 +57,10 @@ struct pb_ctx {
     // timings
     cudaEvent_t ev[4]{};
     double ms_local = 0, ms_scatter = 0, ms_pcg = 0;
+    // pipelined steps (pb_assemble_pipelined): copy streams and their events
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;
+    bool pipe_in_flight = false, out_pending = false, step_timed = false;
     size_t alloc_bytes = 0;
 };
 
@@ -67,6 +71,8 @@ static pb_status fail(pb_ctx* c, pb_status st, const char* fmt, ...) {
 }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 #define NEED(cond, st, msg) do { if (!(cond)) return fail(ctx, st, "%s", msg); } while (0)
+// entry points that read or overwrite buffers of a pipelined step first wait for the steps still in flight
+#define DRAIN() do { if (ctx->pipe_in_flight) { pb_status st_ = pb_pipeline_sync(ctx); if (st_ != PB_OK) return st_; } } while (0)
 
 template <typename T> static cudaError_t dalloc(pb_ctx* c, T** p, size_t n) {
     if (*p) { cudaFree(*p); *p = nullptr; }
@@ -160,6 +166,8 @@ extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->stiff_tab); dfree(&ctx->cg);
     dist_release(ctx);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->ev_in) cudaEventDestroy(ctx->ev_in); if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
+    if (ctx->s_in) cudaStreamDestroy(ctx->s_in); if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx; return PB_OK;
 }
@@ -219,6 +227,7 @@ extern "C" pb_status pb_mesh_get_points(pb_ctx* ctx, double* xy) {
 extern "C" pb_status pb_mesh_set_points(pb_ctx* ctx, const double* xy) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->have_mesh && xy, PB_ERR_STATE, "pb_mesh_set_points: no mesh");
+    DRAIN();
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemcpy(ctx->points, xy, (size_t)ctx->npoints * 16, cudaMemcpyHostToDevice)); ctx->assembled = false; return PB_OK;
 }
@@ -385,8 +394,10 @@ static pb_status scatter_system(pb_ctx* ctx) {
     return PB_OK;
 }
 
-extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
-    if (!ctx) return PB_ERR_INVALID;
+// stages 1+2 of one step.  host_points / host_rhs (pinned, may be null) turn the step into a pipelined one: the
+// vertex upload runs on its own stream as soon as the previous step's local-operator kernel has released the vertex
+// array, the read-back of the condensed rhs on another one after K3, and the next step's K3 waits for that read-back.
+static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const double* host_points, double* host_rhs, bool sync) {
     NEED(ctx->have_mesh && p, PB_ERR_STATE, "pb_assemble: no mesh");
     CK(cudaSetDevice(ctx->device));
     int cd = p->cell_degree, fd = p->face_degree;
@@ -419,6 +430,13 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
     A.ncells = nc; A.fun = p->fun; A.problem = p->problem; A.eta = p->eta;
     A.S = ctx->S; A.g = ctx->g; A.recA = ctx->recA; A.recb = ctx->recb;
     A.lc = p->keep_local ? ctx->lc : nullptr; A.oper = p->keep_local ? ctx->oper : nullptr; A.rhs = p->keep_local ? ctx->rhsloc : nullptr;
+    if (host_points) {
+        if (!ctx->s_in) { CK(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming)); }
+        if (ctx->pipe_in_flight) CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev[1], 0));      // previous K1 has read the vertices
+        CK(cudaMemcpyAsync(ctx->points, host_points, (size_t)ctx->npoints * 16, cudaMemcpyHostToDevice, ctx->s_in));
+        CK(cudaEventRecord(ctx->ev_in, ctx->s_in));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0));
+    }
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     bool found = false;
     CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
@@ -428,13 +446,42 @@ extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
         pb_status st = launch_cut(ctx, A, cd, fd); if (st != PB_OK) return st;
     }
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    if (ctx->out_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_out, 0));         // previous rhs read-back done before K3 overwrites rhs
     { pb_status st = scatter_system(ctx); if (st != PB_OK) return st; }
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_local = ms;
-    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->ms_scatter = ms;
+    if (host_rhs) {
+        if (!ctx->s_out) { CK(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming)); }
+        CK(cudaStreamWaitEvent(ctx->s_out, ctx->ev[2], 0));
+        CK(cudaMemcpyAsync(host_rhs, ctx->rhs, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->s_out));
+        CK(cudaEventRecord(ctx->ev_out, ctx->s_out));
+        ctx->out_pending = true;
+    }
+    ctx->pipe_in_flight = !sync; ctx->step_timed = true;
     ctx->assembled = true;
+    if (sync) return pb_pipeline_sync(ctx);
     return PB_OK;
+}
+extern "C" pb_status pb_pipeline_sync(pb_ctx* ctx) {
+    if (!ctx) return PB_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->s_out) CK(cudaStreamSynchronize(ctx->s_out));
+    ctx->pipe_in_flight = false; ctx->out_pending = false;
+    if (ctx->step_timed) {
+        ctx->step_timed = false;
+        float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_local = ms;
+        cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->ms_scatter = ms;
+    }
+    return PB_OK;
+}
+extern "C" pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* p) {
+    if (!ctx) return PB_ERR_INVALID;
+    if (ctx->pipe_in_flight) { pb_status st = pb_pipeline_sync(ctx); if (st != PB_OK) return st; }
+    return assemble_step(ctx, p, nullptr, nullptr, true);
+}
+extern "C" pb_status pb_assemble_pipelined(pb_ctx* ctx, const pb_assembly_params* p, const double* host_points, double* host_rhs) {
+    if (!ctx) return PB_ERR_INVALID;
+    return assemble_step(ctx, p, host_points, host_rhs, false);
 }
 
 extern "C" pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long long* n_cells, long long* n_local) {
@@ -446,6 +493,7 @@ extern "C" pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* 
 extern "C" pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled, PB_ERR_STATE, "pb_get_csr: nothing assembled");
+    DRAIN();
     CK(cudaSetDevice(ctx->device));
     if (rowptr) CK(cudaMemcpy(rowptr, ctx->rowptr, (size_t)(ctx->nrows + 1) * 8, cudaMemcpyDeviceToHost));
     if (col) CK(cudaMemcpy(col, ctx->col, (size_t)ctx->nnz * 4, cudaMemcpyDeviceToHost));
@@ -456,6 +504,7 @@ extern "C" pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double
 extern "C" pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, long long count, double* out) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && out, PB_ERR_STATE, "pb_get_local: nothing assembled");
+    DRAIN();
     NEED(cell_begin >= 0 && count >= 0 && cell_begin + count <= ctx->ncells_local, PB_ERR_INVALID, "pb_get_local: cell range out of bounds");
     const double* src = nullptr; long long per = 0;
     switch (what) {

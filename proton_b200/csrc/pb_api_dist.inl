@@ -115,6 +115,7 @@ static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 
 extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && p, PB_ERR_STATE, "pb_pcg: nothing assembled");
+    DRAIN();
     const bool whole = ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid);
     NEED(whole || (ctx->world > 1 && ctx->comm), PB_ERR_STATE, "pb_pcg: this context owns a strip: call pb_dist_init on every rank first");
     CK(cudaSetDevice(ctx->device));
