@@ -49,7 +49,9 @@ typedef struct {
     int keep_local;                    /* 1: also keep oper / (data+stab) / rhs per cell for pb_get_local */
 } pb_assembly_params;
 
-/* cg_params (solver_cg.hpp:44-61) */
+/* cg_params (solver_cg.hpp:44-61).  apply_preconditioner: 0 = none, 1 = the reference's diagonal preconditioner
+ * (solver_cg.hpp:78-81), 2 = fbs x fbs block-Jacobi (inverse of every face's diagonal block; an extension with no
+ * reference counterpart: same solution to the tolerance, fewer iterations for face degree >= 2). */
 typedef struct { double convergence_threshold, divergence_threshold; long long max_iter; int apply_preconditioner; } pb_cg_params;
 
 typedef struct { long long iterations; double relative_residual; int exit_reason; double seconds; } pb_cg_result;
@@ -98,13 +100,17 @@ pb_status pb_cut_download(pb_ctx* ctx, int* node_location, int* face_location, d
 pb_status pb_assemble(pb_ctx* ctx, const pb_assembly_params* params);
 /* The same step for a caller that streams meshes through the device (the driver loop of convergence_test.cpp:186-199
  * repeated over a mesh sequence; no counterpart in the serial reference).  Returns after enqueueing:
- *   host_points (page-locked, 2*num_points doubles, may be NULL) is uploaded on a copy stream as soon as the previous
+ *   host_points (page-locked, the whole-mesh array of 2*num_points doubles, may be NULL; a strip context reads only
+ *   pb_strip_point_range of it) is uploaded on a copy stream as soon as the previous
  *   step's local-operator kernel has released the vertex array;
  *   host_rhs (page-locked, n_rows doubles, may be NULL) receives assembler.RHS on a second copy stream after the scatter;
  *   the next step's scatter waits for that read-back.  The caller must not reuse host_rhs before pb_pipeline_sync or
  *   two further steps, and calls pb_pipeline_sync before reading results (the other entry points do it themselves). */
 pb_status pb_assemble_pipelined(pb_ctx* ctx, const pb_assembly_params* params, const double* host_points, double* host_rhs);
 pb_status pb_pipeline_sync(pb_ctx* ctx);
+/* the vertices a strip context reads (those of its own cell rows and the ghost row): points [first, first+count) of the
+ * whole-mesh array; pb_assemble_pipelined uploads exactly this range from host_points */
+pb_status pb_strip_point_range(pb_ctx* ctx, long long* first, long long* count);
 pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long long* n_cells, long long* n_local);
 /* assembler.LHS / assembler.RHS of the condensed system, CSR with sorted columns */
 pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs);
@@ -153,6 +159,17 @@ pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsigned char id[
 /* back-substitution on a strip: cell dofs of the OWNED cell rows only ([row_begin,row_end) x Nx x cbs) and the owned
  * face dofs */
 pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
+
+/* ---- driver outputs.
+ * pb_pcg_history(capacity > 0): the following pb_pcg calls record nr/nr0 exactly where conjugated_gradient writes a line
+ * to cg_params::histfile (solver_cg.hpp:92-93, 101-102, 133-137): entry 0 = 1, entry i = relative residual after i
+ * updates, the closing line included, iterations + 2 entries in all; capacity 0 switches it off.
+ * pb_sample_solution: the rows "x y value" of the driver's solution_N_<N>_k_<k>.dat (convergence_test.cpp:250-252,
+ * 280-286) for the owned cells: cell solution at the degree-2*cell_degree quadrature points, cells ascending, points in
+ * integrate()'s order; xyv = 3 doubles per point (NULL: only *n_points is set). ---- */
+pb_status pb_pcg_history(pb_ctx* ctx, long long capacity);
+pb_status pb_pcg_get_history(pb_ctx* ctx, double* out, long long capacity, long long* n);
+pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points);
 
 /* ---- measurement hooks (bench.py): device-side timing of the last pb_assemble / pb_pcg, milliseconds ---- */
 pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg);

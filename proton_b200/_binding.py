@@ -68,6 +68,9 @@ def lib():
         L.pb_get_local.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
         L.pb_assemble_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pb_pipeline_sync.argtypes = [C.c_void_p]
+        L.pb_pcg_history.argtypes = [C.c_void_p, C.c_longlong]
+        L.pb_pcg_get_history.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
+        L.pb_sample_solution.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
         _lib = L
     return _lib
 
@@ -231,6 +234,11 @@ class Context:
         self.hdi = hdi
         return self
 
+    def strip_point_range(self):
+        a = C.c_longlong(); b = C.c_longlong()
+        self._ck(lib().pb_strip_point_range(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def pipeline_sync(self):
         self._ck(lib().pb_pipeline_sync(self._h))
         return self
@@ -259,10 +267,31 @@ class Context:
     # ---- stage 3
     def conjugated_gradient(self, cgp=None):
         cgp = cgp or cg_params()
-        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(bool(cgp.apply_preconditioner)))
+        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(cgp.apply_preconditioner))
         r = _CgResult()
         self._ck(lib().pb_pcg(self._h, C.byref(p), C.byref(r)))
         return dict(iterations=r.iterations, relative_residual=r.relative_residual, exit_reason=r.exit_reason, seconds=r.seconds)
+
+    # ---- driver outputs
+    def pcg_history(self, capacity):
+        """record the histfile lines of the following conjugated_gradient calls (0 switches it off)"""
+        self._ck(lib().pb_pcg_history(self._h, C.c_longlong(int(capacity)))); return self
+
+    def history(self):
+        n = C.c_longlong()
+        self._ck(lib().pb_pcg_get_history(self._h, None, C.c_longlong(0), C.byref(n)))
+        out = np.zeros(n.value)
+        if n.value:
+            self._ck(lib().pb_pcg_get_history(self._h, _ptr(out), C.c_longlong(n.value), C.byref(n)))
+        return out
+
+    def sample_solution(self):
+        """rows (x, y, u_T) of the driver's solution_N_*_k_*.dat for the owned cells"""
+        n = C.c_longlong()
+        self._ck(lib().pb_sample_solution(self._h, None, C.c_longlong(0), C.byref(n)))
+        out = np.zeros((n.value, 3))
+        self._ck(lib().pb_sample_solution(self._h, _ptr(out), C.c_longlong(n.value), C.byref(n)))
+        return out
 
     def face_solution(self):
         x = np.zeros(self.n_rows); self._ck(lib().pb_get_face_solution(self._h, _ptr(x))); return x
@@ -286,7 +315,7 @@ class Context:
         self.n_rows, self.nnz, self.ncells_local, self.n_local = n.value, nnz.value, nc.value, nl.value
 
     def obstacle_iterate(self, cgp):
-        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(bool(cgp.apply_preconditioner)))
+        p = _CgParams(cgp.convergence_threshold, cgp.divergence_threshold, int(cgp.max_iter), int(cgp.apply_preconditioner))
         d = C.c_double(); na = C.c_longlong(); it = C.c_longlong()
         self._ck(lib().pb_obstacle_iterate(self._h, C.byref(p), C.byref(d), C.byref(na), C.byref(it)))
         return d.value, na.value, it.value

@@ -47,7 +47,7 @@ struct pb_ctx {
     BlockRow* brows = nullptr; long long* brp = nullptr;
     long long* rowptr = nullptr; int* col = nullptr; double *val = nullptr, *rhs = nullptr;
     // solver
-    double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *parts = nullptr;
+    double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *iAb = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
     double *dfull = nullptr, *scal = nullptr;      // d with halos (d = dfull + halo_lo); all-reduced scalars
     // obstacle active-set state (per cell)
@@ -61,6 +61,8 @@ struct pb_ctx {
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in = nullptr, ev_out = nullptr;
     bool pipe_in_flight = false, out_pending = false, step_timed = false;
+    // residual history of the last pb_pcg (pb_pcg_history)
+    double* hist = nullptr; long long hist_cap = 0, hist_n = 0;
     size_t alloc_bytes = 0;
 };
 
@@ -149,7 +151,7 @@ extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
-    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->parts); dfree(&c->scal);
+    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->iAb); dfree(&c->parts); dfree(&c->scal);
     dfree(&c->ob_alpha); dfree(&c->ob_beta); dfree(&c->ob_gamma); dfree(&c->ob_xprev); dfree(&c->ob_inA); c->ob_ready = false;
     c->assembled = false;
 }
@@ -163,7 +165,7 @@ static void free_cut(pb_ctx* c) {
 extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     if (!ctx) return PB_OK;
     cudaSetDevice(ctx->device);
-    free_system(ctx); free_cut(ctx); dfree(&ctx->points); dfree(&ctx->stiff_tab); dfree(&ctx->cg);
+    free_system(ctx); free_cut(ctx); dfree(&ctx->hist); dfree(&ctx->points); dfree(&ctx->stiff_tab); dfree(&ctx->cg);
     dist_release(ctx);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->ev_in) cudaEventDestroy(ctx->ev_in); if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
@@ -433,7 +435,9 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     if (host_points) {
         if (!ctx->s_in) { CK(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming)); }
         if (ctx->pipe_in_flight) CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev[1], 0));      // previous K1 has read the vertices
-        CK(cudaMemcpyAsync(ctx->points, host_points, (size_t)ctx->npoints * 16, cudaMemcpyHostToDevice, ctx->s_in));
+        // host_points is the whole-mesh array; a strip context reads only the vertex rows of its own cells
+        const long long p0 = ctx->strip.cell_row0 * (ctx->grid.Nx + 1), pn = (ctx->grid.row_end - ctx->strip.cell_row0 + 1) * (ctx->grid.Nx + 1);
+        CK(cudaMemcpyAsync(ctx->points + p0, host_points + 2 * p0, (size_t)pn * 16, cudaMemcpyHostToDevice, ctx->s_in));
         CK(cudaEventRecord(ctx->ev_in, ctx->s_in));
         CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0));
     }
@@ -459,6 +463,12 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     ctx->pipe_in_flight = !sync; ctx->step_timed = true;
     ctx->assembled = true;
     if (sync) return pb_pipeline_sync(ctx);
+    return PB_OK;
+}
+extern "C" pb_status pb_strip_point_range(pb_ctx* ctx, long long* first, long long* count) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_mesh && first && count, PB_ERR_STATE, "pb_strip_point_range: no mesh");
+    *first = ctx->strip.cell_row0 * (ctx->grid.Nx + 1); *count = (ctx->grid.row_end - ctx->strip.cell_row0 + 1) * (ctx->grid.Nx + 1);
     return PB_OK;
 }
 extern "C" pb_status pb_pipeline_sync(pb_ctx* ctx) {

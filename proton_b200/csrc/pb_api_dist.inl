@@ -138,6 +138,9 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     const double *c_dy = multi ? s_dy : p_dy, *c_rr = multi ? s_rr : p_rr, *c_rz = multi ? s_rz : p_rz;
     const int c_n = multi ? 1 : nblk;
     const int pre = p->apply_preconditioner ? 1 : 0;
+    const bool blockpre = p->apply_preconditioner == 2 && F >= 2 && F <= 4;      // F = 1: the block is the diagonal
+    if (blockpre && !ctx->iAb) CK(dalloc(ctx, &ctx->iAb, (size_t)n * F));
+    const long long nbr_own = n / F;
     const int lpr = spmv_lanes(F);
     const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1;   // scalar CSR: comparison runs, and F = 1 where a
                                                                                // 64-byte face record per row costs more than 7 column indices
@@ -157,10 +160,17 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     };
     auto t0 = std::chrono::steady_clock::now();
     CK(cudaEventRecord(ctx->ev[0], sm));
-    pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
-    pcg_init_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
+    if (blockpre) {
+#define PB_BJ(F_) do { pcg_bdiag_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iAb); \
+        pcg_init_blk_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, ctx->rhs, ctx->iAb, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz); } while (0)
+        if (F == 2) PB_BJ(2); else if (F == 3) PB_BJ(3); else PB_BJ(4);
+#undef PB_BJ
+    } else {
+        pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
+        pcg_init_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
+    }
     { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
-    pcg_init_state_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, ctx->cg);
+    pcg_init_state_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, ctx->cg, ctx->hist);
     CK(cudaGetLastError());
     // one iteration = [dir, commit] (skipped in the very first one), halo exchange, spmv, xrz (+ all-reduces)
     auto spmv_xrz = [&]() -> pb_status {
@@ -180,12 +190,17 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
             pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk_sp, p_dy, s_dy, nullptr, nullptr);
             NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
         }
-        pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, c_ndy, c_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
+        if (blockpre) {
+#define PB_BJ(F_) pcg_xrz_blk_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, c_ndy, c_dy, ctx->iAb, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg)
+            if (F == 2) PB_BJ(2); else if (F == 3) PB_BJ(3); else PB_BJ(4);
+#undef PB_BJ
+        } else
+            pcg_xrz_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, c_ndy, c_dy, ctx->iA, ctx->d, ctx->y, ctx->x, ctx->r, ctx->z, p_rr, p_rz, ctx->cg);
         return reduce_rr_rz();
     };
     auto full_iteration = [&]() -> pb_status {
         pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, ctx->z, ctx->d, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
-        pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
+        pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg, ctx->hist, ctx->hist_cap);
         return spmv_xrz();
     };
     CgState hs{}; const int check_every = 32;
@@ -214,10 +229,29 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     if (gexec) { cudaGraphExecDestroy(gexec); cudaGraphDestroy(graph); }
     CK(cudaEventRecord(ctx->ev[1], sm)); CK(cudaStreamSynchronize(sm));
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
+    ctx->hist_n = ctx->hist ? std::min<long long>(hs.iters + 2, ctx->hist_cap) : 0;
     if (res) {
         res->iterations = hs.iters; res->relative_residual = hs.relres; res->exit_reason = hs.reason;
         res->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     }
+    return PB_OK;
+}
+
+// residual history = the lines conjugated_gradient writes to cg_params::histfile (solver_cg.hpp:92-93, 101-102, 133-137)
+extern "C" pb_status pb_pcg_history(pb_ctx* ctx, long long capacity) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(capacity >= 0, PB_ERR_INVALID, "pb_pcg_history: negative capacity");
+    CK(cudaSetDevice(ctx->device));
+    dfree(&ctx->hist); ctx->hist_cap = 0; ctx->hist_n = 0;
+    if (capacity > 0) { CK(dalloc(ctx, &ctx->hist, (size_t)capacity)); ctx->hist_cap = capacity; }
+    return PB_OK;
+}
+extern "C" pb_status pb_pcg_get_history(pb_ctx* ctx, double* out, long long capacity, long long* n) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(n, PB_ERR_INVALID, "pb_pcg_get_history: null count");
+    CK(cudaSetDevice(ctx->device));
+    *n = ctx->hist_n;
+    if (out && ctx->hist_n > 0) CK(cudaMemcpy(out, ctx->hist, (size_t)std::min(capacity, ctx->hist_n) * 8, cudaMemcpyDeviceToHost));
     return PB_OK;
 }
 
@@ -271,6 +305,38 @@ static cudaError_t launch_norms_t(pb_ctx* c, NormArgs& A, int grid) {
     if (e != cudaSuccess) return e;
     kern<<<grid, 32, smem, c->stream>>>(A);
     return cudaGetLastError();
+}
+
+// the driver's solution_N_*_k_*.dat (convergence_test.cpp:250-252, 280-286): cell solution at the degree-2*cd points
+extern "C" pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && n_points, PB_ERR_STATE, "pb_sample_solution: no face solution");
+    NEED(ctx->prm.problem == PB_PROBLEM_HHO, PB_ERR_UNSUPPORTED, "pb_sample_solution: uncut HHO problems only");
+    CK(cudaSetDevice(ctx->device));
+    const int cd = ctx->CD, qk = ctx->quad_kind;
+    NEED(cd >= 0 && cd <= 4, PB_ERR_UNSUPPORTED, "pb_sample_solution: cell degree > 4");
+    const Grid& g = ctx->grid;
+    const long long owned = (g.row_end - g.row_begin) * g.Nx;
+    const long long nq = sample_points_per_cell(cd, qk);
+    *n_points = owned * nq;
+    if (!xyv) return PB_OK;
+    NEED(capacity_points >= owned * nq, PB_ERR_INVALID, "pb_sample_solution: buffer too small");
+    double *uc = nullptr, *xfull = nullptr;
+    pb_status st = recover_owned(ctx, nullptr, &uc, &xfull); if (st != PB_OK) return st;
+    cudaFree(xfull);
+    double* out = nullptr; CK(cudaMalloc((void**)&out, (size_t)owned * nq * 24));
+    const unsigned grid = (unsigned)std::min<long long>((owned * nq + 255) / 256, 148 * 64);
+    bool ok = true;
+#define PB_SMP(CD_) case CD_: if (qk == 0) sample_solution_kernel<CD_, 0><<<grid, 256, 0, ctx->stream>>>(g, ctx->points, uc, out); \
+                             else sample_solution_kernel<CD_, 1><<<grid, 256, 0, ctx->stream>>>(g, ctx->points, uc, out); break;
+    switch (cd) { PB_SMP(0) PB_SMP(1) PB_SMP(2) PB_SMP(3) PB_SMP(4) default: ok = false; }
+#undef PB_SMP
+    cudaError_t e = ok ? cudaGetLastError() : cudaErrorInvalidValue;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xyv, out, (size_t)owned * nq * 24, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(out); cudaFree(uc);
+    if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_sample_solution: %s", cudaGetErrorString(e));
+    return PB_OK;
 }
 
 extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {

@@ -260,4 +260,29 @@ __global__ void __launch_bounds__(32) error_norms_kernel(NormArgs A) {
     if (lane == 0) { A.parts[3 * blockIdx.x] = sum0; A.parts[3 * blockIdx.x + 1] = sum1; A.parts[3 * blockIdx.x + 2] = sum2; }
 }
 
+// ---- solution_N_*_k_*.dat of the driver (convergence_test.cpp:250-252, 280-286): (x, y, u_T(x, y)) at the degree-2*cd
+// points of every owned cell, cells ascending, points in integrate()'s order.  One thread per point.
+inline long long sample_points_per_cell(int cd, int qk) { return qk == PB_QUAD_TENSOR_GAUSS ? cell_qps(PB_QUAD_TENSOR_GAUSS, 2 * cd) : cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * cd); }
+template <int CD, int QK>
+__global__ void sample_solution_kernel(Grid g, const double2* __restrict__ points, const double* __restrict__ ucell, double* __restrict__ out) {
+    constexpr int C = (CD + 1) * (CD + 2) / 2, nq = cell_qps(QK, 2 * CD);
+    const long long total = (g.row_end - g.row_begin) * g.Nx * nq;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long lc = t / nq; const int q = (int)(t - lc * nq);
+        const long long ci = lc % g.Nx, cj = g.row_begin + lc / g.Nx, p0 = grid_point(g, ci, cj);
+        const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
+        CellGeom geo;
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const double2 v = points[pid[i]]; geo.vx[i] = v.x; geo.vy[i] = v.y; }
+        cell_geometry(geo);
+        double x, y, w; cell_qp<QK, 2 * CD>(geo, q, x, y, w);
+        double phi[C], dx[C], dy[C];
+        eval_cell_basis<CD>((x - geo.barx) * geo.ihalf, (y - geo.bary) * geo.ihalf, geo.ihalf, phi, dx, dy);
+        double val = 0.0;
+#pragma unroll
+        for (int c = 0; c < C; c++) val += ucell[lc * C + c] * phi[c];
+        out[3 * t] = x; out[3 * t + 1] = y; out[3 * t + 2] = val;
+    }
+}
+
 }  // namespace pb

@@ -83,7 +83,8 @@ __global__ void pcg_init_kernel(long long n, int precond, const double* __restri
     double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
     t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
 }
-__global__ void pcg_init_state_kernel(int nparts, const double* parts_rr, const double* parts_rz, CgState* st) {
+__global__ void pcg_init_state_kernel(int nparts, const double* parts_rr, const double* parts_rz, CgState* st, double* hist = nullptr) {
+    if (hist && threadIdx.x == 0) hist[0] = 1.0;                 // nr/nr0 printed at the top of iteration 0 (solver_cg.hpp:101-102)
     __shared__ double sh[32];
     double rr = reduce_partials(parts_rr, nparts, sh), rz = reduce_partials(parts_rz, nparts, sh);
     if (threadIdx.x == 0) { st->rho = rz; st->nr0 = sqrt(rr); st->relres = 1.0; st->iters = 0; st->done = 0; st->reason = PB_CG_MAX_ITER_REACHED; }
@@ -185,6 +186,96 @@ __global__ void pcg_xrz_kernel(long long n, int precond, int nparts, const doubl
     t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
 }
 
+// ---- optional F x F block-Jacobi preconditioner (apply_preconditioner = 2; NOT reference behaviour: the reference only
+// knows the diagonal, solver_cg.hpp:78-81).  iAb[br] = inverse of the diagonal block of face br, row-major.
+template <int F>
+__global__ void pcg_bdiag_kernel(long long nbr, long long row0, const long long* __restrict__ rowptr, const int* __restrict__ col,
+                                 const double* __restrict__ val, double* __restrict__ iAb) {
+    for (long long br = blockIdx.x * (long long)blockDim.x + threadIdx.x; br < nbr; br += (long long)gridDim.x * blockDim.x) {
+        double A[F][F], B[F][F];
+        const int want = (int)(row0 + br * F);
+#pragma unroll
+        for (int a = 0; a < F; a++) {
+            const long long k0 = rowptr[br * F + a], k1 = rowptr[br * F + a + 1];
+            long long kd = k0;
+            for (long long k = k0; k < k1; k += F) if (col[k] == want) kd = k;      // column blocks are F wide and sorted
+#pragma unroll
+            for (int c = 0; c < F; c++) { A[a][c] = val[kd + c]; B[a][c] = a == c ? 1.0 : 0.0; }
+        }
+        // Gauss-Jordan without pivoting (the block is symmetric positive definite)
+#pragma unroll
+        for (int k = 0; k < F; k++) {
+            const double ip = 1.0 / A[k][k];
+#pragma unroll
+            for (int c = 0; c < F; c++) { A[k][c] *= ip; B[k][c] *= ip; }
+#pragma unroll
+            for (int a = 0; a < F; a++) {
+                if (a == k) continue;
+                const double f = A[a][k];
+#pragma unroll
+                for (int c = 0; c < F; c++) { A[a][c] -= f * A[k][c]; B[a][c] -= f * B[k][c]; }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < F; a++)
+#pragma unroll
+            for (int c = 0; c < F; c++) iAb[br * (F * F) + a * F + c] = 0.5 * (B[a][c] + B[c][a]);    // exactly symmetric
+    }
+}
+// one thread per face: x = 0, r = b, z = iAb r, d = z
+template <int F>
+__global__ void pcg_init_blk_kernel(long long nbr, const double* __restrict__ b, const double* __restrict__ iAb,
+                                    double* __restrict__ x, double* __restrict__ r, double* __restrict__ z, double* __restrict__ d,
+                                    double* __restrict__ parts_rr, double* __restrict__ parts_rz) {
+    __shared__ double sh[32];
+    double rr = 0.0, rz = 0.0;
+    for (long long br = blockIdx.x * (long long)blockDim.x + threadIdx.x; br < nbr; br += (long long)gridDim.x * blockDim.x) {
+        double ri[F];
+#pragma unroll
+        for (int a = 0; a < F; a++) ri[a] = b[br * F + a];
+#pragma unroll
+        for (int a = 0; a < F; a++) {
+            double zi = 0.0;
+#pragma unroll
+            for (int c = 0; c < F; c++) zi += iAb[br * (F * F) + a * F + c] * ri[c];
+            x[br * F + a] = 0.0; r[br * F + a] = ri[a]; z[br * F + a] = zi; d[br * F + a] = zi;
+            rr += ri[a] * ri[a]; rz += ri[a] * zi;
+        }
+    }
+    double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
+    t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
+}
+template <int F>
+__global__ void pcg_xrz_blk_kernel(long long nbr, int nparts, const double* __restrict__ parts_dy, const double* __restrict__ iAb,
+                                   const double* __restrict__ d, const double* __restrict__ y, double* __restrict__ x, double* __restrict__ r,
+                                   double* __restrict__ z, double* __restrict__ parts_rr, double* __restrict__ parts_rz, const CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    double dy = reduce_partials(parts_dy, nparts, sh);
+    double alpha = st->rho / dy;
+    double rr = 0.0, rz = 0.0;
+    for (long long br = blockIdx.x * (long long)blockDim.x + threadIdx.x; br < nbr; br += (long long)gridDim.x * blockDim.x) {
+        double ri[F];
+#pragma unroll
+        for (int a = 0; a < F; a++) {
+            const long long i = br * F + a;
+            x[i] = x[i] + alpha * d[i];
+            ri[a] = r[i] - alpha * y[i];
+            r[i] = ri[a];
+        }
+#pragma unroll
+        for (int a = 0; a < F; a++) {
+            double zi = 0.0;
+#pragma unroll
+            for (int c = 0; c < F; c++) zi += iAb[br * (F * F) + a * F + c] * ri[c];
+            z[br * F + a] = zi;
+            rr += ri[a] * ri[a]; rz += ri[a] * zi;
+        }
+    }
+    double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
+    t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
+}
+
 // exit tests in the reference's order (solver_cg.hpp:112-125), then beta = (r.z)/rho, d = z + beta d, iter++.
 // st->iters = number of completed direction updates before this call.
 __global__ void pcg_dir_kernel(long long n, int nparts, const double* __restrict__ parts_rr, const double* __restrict__ parts_rz,
@@ -209,7 +300,7 @@ __global__ void pcg_dir_kernel(long long n, int nparts, const double* __restrict
 }
 // single-block bookkeeping after pcg_dir_kernel: same decisions, written once
 __global__ void pcg_commit_kernel(int nparts, const double* parts_rr, const double* parts_rz, double tol, double divtol,
-                                  long long max_iter, CgState* st) {
+                                  long long max_iter, CgState* st, double* hist = nullptr, long long hist_cap = 0) {
     __shared__ double sh[32];
     if (st->done) return;
     const long long iter = st->iters;
@@ -221,6 +312,7 @@ __global__ void pcg_commit_kernel(int nparts, const double* parts_rr, const doub
     else if (iter > max_iter) reason = PB_CG_MAX_ITER_REACHED;
     else if (rel > divtol) reason = PB_CG_DIVERGED;
     st->relres = rel;
+    if (hist && iter + 1 < hist_cap) hist[iter + 1] = rel;       // the histfile line of iteration iter+1 (or the closing line)
     if (reason >= 0) { st->done = 1; st->reason = reason; st->iters = iter; }
     else { st->rho = rz; st->iters = iter + 1; }
 }

@@ -39,6 +39,13 @@ def main():
             print(f"N={Nx}x{Ny} k={k} world={world}: iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, rel diff {err:.2e}", flush=True)
             ok = ok and err < 1e-9 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2
             ref.close()
+        # block-Jacobi extension (apply_preconditioner = 2) on strips: same solution as the diagonal preconditioner
+        rb = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 10000, 2))
+        cells_b, faces_b = ctx.recover_strip(ctx.row_begin, ctx.row_end)
+        okb = rb["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_b - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        if not okb:
+            print(f"rank {rank}: block-Jacobi solve differs (N={Nx}x{Ny} k={k}): {rb}", flush=True)
+        ok = ok and okb
         ctx.close()
     # fictitious-domain problem (cut cells by K2): every rank preprocesses the whole level set, assembles its strip
     for (N, k) in [(20, 1), (24, 2)]:
@@ -64,7 +71,8 @@ def main():
             ref.close()
         ctx.close()
     flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
-    dist.broadcast(flag, 0)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = bool(int(flag))
     dist.destroy_process_group()
     if rank == 0:
         print("DIST CHECK", "PASSED" if ok else "FAILED", flush=True)

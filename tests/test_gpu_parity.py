@@ -110,6 +110,80 @@ def test_pcg_solution_matches_full_system_direct_solve(ctx, k, N):
     assert np.max(np.abs(e_dev - e_ref) / e_ref) < TOL_SOL, (e_dev, e_ref)
 
 
+@pytest.mark.parametrize("k,N", [(1, 24), (2, 24), (3, 16)])
+def test_block_jacobi_extension_same_solution_fewer_iterations(ctx, k, N):
+    """apply_preconditioner = 2 (fbs x fbs block-Jacobi, no reference counterpart): same discrete solution as the
+    reference's diagonal preconditioner to 1e-8, never more iterations (the tanh data make the solve a generic one)."""
+    ctx.mesh(pb.mesh_init_params(N, N))
+    ctx.assemble(pb.hho_degree_info(k + 1, k), fun=PB.FUN_TANH)
+    r1 = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 20000, 1)); x1 = ctx.recover()
+    r2 = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 20000, 2)); x2 = ctx.recover()
+    assert r1["exit_reason"] == PB.CG_CONVERGED and r2["exit_reason"] == PB.CG_CONVERGED
+    assert np.linalg.norm(x1 - x2) / np.linalg.norm(x1) < TOL_SOL
+    assert r2["iterations"] <= r1["iterations"]
+    if k >= 2:
+        assert r2["iterations"] < 0.9 * r1["iterations"], (r1["iterations"], r2["iterations"])
+
+
+def _cg_history_numpy(A, b, tol, max_iter, precond):
+    """the lines conjugated_gradient writes to cg_params::histfile (solver_cg.hpp:63-144), restated with numpy"""
+    x = np.zeros_like(b); iA = 1.0 / A.diagonal()
+    r = b - A @ x; d = iA * r if precond else r.copy(); nr0 = nr = np.linalg.norm(r); hist = []; it = 0
+    while True:
+        hist.append(nr / nr0)
+        y = A @ d; iMr = iA * r if precond else r; rho = r @ iMr; alpha = rho / (d @ y)
+        x = x + alpha * d; r = r - alpha * y; nr = np.linalg.norm(r)
+        if nr / nr0 < tol or it > max_iter or nr / nr0 > 1e300:
+            break
+        iMr = iA * r if precond else r; d = iMr + (r @ iMr) / rho * d; it += 1
+    hist.append(nr / nr0)
+    return np.array(hist), it
+
+
+@pytest.mark.parametrize("precond", [True, False])
+def test_residual_history_matches_histfile_lines(ctx, precond):
+    N, k = 20, 2
+    ctx.mesh(pb.mesh_init_params(N, N)).assemble(pb.hho_degree_info(k + 1, k), fun=PB.FUN_TANH)
+    rp, col, val, rhs = ctx.csr()
+    A = sp.csr_matrix((val, col, rp), shape=(len(rhs), len(rhs)))
+    want, it = _cg_history_numpy(A, rhs, 1e-10, 3 * len(rhs), precond)
+    ctx.pcg_history(4 * len(rhs))
+    res = ctx.conjugated_gradient(pb.cg_params(1e-10, 1e300, 3 * len(rhs), precond))
+    got = ctx.history()
+    ctx.pcg_history(0)
+    assert res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - it) <= 1
+    assert len(got) == res["iterations"] + 2 and got[0] == 1.0 and got[-1] == res["relative_residual"]
+    m = min(len(got), len(want)) - 2          # the last lines sit at the tolerance, where rounding decides the count
+    rel = np.abs(got[:m] - want[:m]) / want[:m]
+    assert np.max(rel[:30]) < 1e-8            # same recurrence: identical to rounding while the iterates still agree
+    assert np.max(rel) < 0.25                 # rounding differences grow along the Krylov recurrence, the curve stays the same
+    assert len(ctx.history()) == 0
+
+
+@pytest.mark.parametrize("k,poly", [(0, False), (1, False), (2, False), (3, False), (1, True), (2, True)])
+def test_solution_samples_match_the_driver_dat_rows(ctx, k, poly):
+    """pb_sample_solution = rows of solution_N_*_k_*.dat (convergence_test.cpp:280-286): oracle quadrature points
+    (integrate(msh, cl, 2*cd)), scaled monomial basis of bases.hpp:70-195 restated here, dofs from pb_recover."""
+    N, cd = 6, k + 1
+    qk = PB.QUAD_POLY_DUNAVANT if poly else PB.QUAD_TENSOR_GAUSS
+    m = orc.Mesh(N, poly=poly)
+    ctx.mesh(pb.mesh_init_params(N, N), qk).assemble(pb.hho_degree_info(cd, k), stab_kind=PB.STAB_NAIVE if poly else PB.STAB_FANCY)
+    ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 20000, True))
+    full = ctx.recover(); C_ = (cd + 1) * (cd + 2) // 2
+    got = ctx.sample_solution()
+    bar = m.barycenters(); h = np.hypot(1.0 / N, 1.0 / N)
+    rows = []
+    for c in range(m.ncells):
+        pts, _ = m.quadrature(c, 2 * cd)
+        bx = (pts[:, 0] - bar[c, 0]) / (0.5 * h); by = (pts[:, 1] - bar[c, 1]) / (0.5 * h)
+        phi = np.stack([bx ** (d - i) * by ** i for d in range(cd + 1) for i in range(d + 1)], axis=1)
+        rows.append(np.column_stack([pts, phi @ full[c * C_:(c + 1) * C_]]))
+    want = np.vstack(rows)
+    assert got.shape == want.shape
+    assert np.max(np.abs(got[:, :2] - want[:, :2])) < 1e-14
+    assert np.max(np.abs(got[:, 2] - want[:, 2])) < 1e-12 * max(1.0, np.max(np.abs(want[:, 2])))
+
+
 def test_pcg_iteration_count_matches_reference_cg(ctx):
     """Same algorithm => same iteration count and residual history end as solver_cg.hpp on the same matrix."""
     N, k = 16, 1
