@@ -14,6 +14,8 @@
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
+#include <fstream>
+#include <iostream>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -54,8 +56,10 @@ struct cg_params {
     T convergence_threshold, divergence_threshold;
     size_t max_iter;
     bool verbose, apply_preconditioner, save_reshist;
+    std::string histfile;               // solver_cg.hpp:51: one line nr/nr0 per iteration + the closing line
+    bool block_preconditioner;          // extension (no reference counterpart): fbs x fbs block-Jacobi instead of the diagonal
     cg_params() : convergence_threshold(1e-9), divergence_threshold(100), max_iter(1000), verbose(false),
-                  apply_preconditioner(false), save_reshist(false) {}
+                  apply_preconditioner(false), save_reshist(false), block_preconditioner(false) {}
 };
 
 // quad_mesh<T>(mip) / cuthho_poly_mesh<T>(mip): the Cartesian generator; cells, faces and the boundary flags are
@@ -157,6 +161,14 @@ public:
     const cartesian_mesh<T>& mesh() const { return msh_; }
     // the drivers' post-processing sums: {L2^2, mass-norm^2, energy^2} (convergence_test.cpp:254-306) or {H1^2, 0, 0}
     // for the fictitious-domain problem (cuthho_square.cpp:1031-1050)
+    // rows "x y value" of the driver's solution_N_<N>_k_<k>.dat (convergence_test.cpp:250-252, 280-286)
+    void write_solution(const std::string& filename) const {
+        long long n = 0; msh_.check(pb_sample_solution(msh_.ctx(), nullptr, 0, &n));
+        std::vector<T> xyv((size_t)3 * n);
+        msh_.check(pb_sample_solution(msh_.ctx(), xyv.data(), n, &n));
+        std::ofstream ofs(filename);
+        for (long long i = 0; i < n; i++) ofs << xyv[3 * i] << " " << xyv[3 * i + 1] << " " << xyv[3 * i + 2] << "\n";
+    }
     std::vector<T> error_norms() const { std::vector<T> out(3); msh_.check(pb_error_norms(msh_.ctx(), out.data())); return out; }
     size_t system_size() const { long long n = 0; msh_.check(pb_system_sizes(msh_.ctx(), &n, nullptr, nullptr, nullptr)); return (size_t)n; }
 };
@@ -167,9 +179,21 @@ assembler<T> make_assembler(const cartesian_mesh<T>& msh, hho_degree_info hdi) {
 // conjugated_gradient(A, b, x, parms): A and b are the device-resident system of `assm`; x receives the face solution
 template <typename T>
 cg_exit_reason conjugated_gradient(const assembler<T>& assm, std::vector<T>& x, const cg_params<T>& parms, size_t* iterations = nullptr) {
-    pb_cg_params p{parms.convergence_threshold, parms.divergence_threshold, (long long)parms.max_iter, parms.apply_preconditioner ? 1 : 0};
+    pb_cg_params p{parms.convergence_threshold, parms.divergence_threshold, (long long)parms.max_iter,
+                   parms.apply_preconditioner ? (parms.block_preconditioner ? 2 : 1) : 0};
     pb_cg_result r{};
+    const bool hist = !parms.histfile.empty();
+    if (hist) assm.mesh().check(pb_pcg_history(assm.mesh().ctx(), (long long)parms.max_iter + 3));
     assm.mesh().check(pb_pcg(assm.mesh().ctx(), &p, &r));
+    if (hist) {         // the same lines, in the same default stream format, as solver_cg.hpp:101-102, 133-137
+        long long nh = 0; assm.mesh().check(pb_pcg_get_history(assm.mesh().ctx(), nullptr, 0, &nh));
+        std::vector<T> h((size_t)nh);
+        if (nh) assm.mesh().check(pb_pcg_get_history(assm.mesh().ctx(), h.data(), nh, &nh));
+        assm.mesh().check(pb_pcg_history(assm.mesh().ctx(), 0));
+        std::ofstream ofs(parms.histfile);
+        for (T v : h) ofs << v << std::endl;
+    }
+    if (parms.verbose) std::cout << " -> Iteration " << r.iterations << ", rr = " << r.relative_residual << std::endl;
     long long n = 0; assm.mesh().check(pb_system_sizes(assm.mesh().ctx(), &n, nullptr, nullptr, nullptr));
     x.resize((size_t)n);
     assm.mesh().check(pb_get_face_solution(assm.mesh().ctx(), x.data()));

@@ -52,9 +52,20 @@ def test_convergence_test_driver_rates(tmp_path):
     _build()
     cfg = tmp_path / "cfg.lua"
     cfg.write_text("-- flat config, the reference's keys\ndeg_min = 1\ndeg_max = 2\nmin_N = 8\nsteps = 3\nprecond = true\nstab_hho = true\n")
-    r = subprocess.run([os.path.join(BIN, "convergence_test"), str(cfg)], capture_output=True, text=True, check=True)
+    r = subprocess.run([os.path.join(BIN, "convergence_test"), str(cfg)], capture_output=True, text=True, check=True, cwd=tmp_path)
     rates = re.findall(r"L2 [0-9.e+-]+ \(([0-9.]+)\)\s+energy [0-9.e+-]+ \(([0-9.]+)\)", r.stdout)
     assert len(rates) == 4
     # HHO(k+1,k): L2 order k+2, energy order k+1 (convergence_test.cpp:312-325)
     for (l2, en), k in zip(rates, (1, 1, 2, 2)):
         assert abs(float(l2) - (k + 2)) < 0.25 and abs(float(en) - (k + 1)) < 0.15
+    # the reference's output files (convergence_test.cpp:155-161, 232-242, 250-252, 311-312)
+    its = [int(v) for v in re.findall(r"CG its (\d+)", r.stdout)]
+    for k in (1, 2):
+        rows = [l.split() for l in (tmp_path / f"hho_history_precond_{k}.txt").read_text().splitlines()]
+        assert len(rows) == 3 and all(len(x) == 3 for x in rows) and abs(float(rows[0][0]) - 2 ** 0.5 / 8) < 1e-6
+        for i, N in enumerate((8, 16, 32)):
+            hist = [float(v) for v in (tmp_path / f"cg_history_precond_{N}_{k}.txt").read_text().split()]
+            assert hist[0] == 1.0 and hist[-1] < 1e-12 and len(hist) == its[(k - 1) * 3 + i] + 2
+            cd = k + 1; nq = ((2 * cd + 2) // 2) ** 2           # tensor Gauss points of degree 2*cd per cell
+            dat = (tmp_path / f"solution_N_{N}_k_{k}.dat").read_text().splitlines()
+            assert len(dat) == N * N * nq and len(dat[0].split()) == 3
