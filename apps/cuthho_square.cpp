@@ -36,6 +36,7 @@ int main(int argc, char** argv) {
         assembler.assemble_all(PB_STAB_CUT, PB_PROBLEM_FICTDOM, PB_FUN_SINSIN, 0, 5.0);
         std::cout << "System unknowns (condensed): " << assembler.system_size() << std::endl;
         pb::cg_params<double> cgp; cgp.apply_preconditioner = true; cgp.convergence_threshold = 1e-13; cgp.max_iter = 20 * assembler.system_size();
+        cgp.histfile = "cuthho_cg_hist.dat";      // as the reference's CG variant of this solve (cuthho_square.cpp:922-928)
         std::vector<double> sol; size_t iters = 0;
         auto er = pb::conjugated_gradient(assembler, sol, cgp, &iters);
         std::cout << "CG iterations: " << iters << (er == pb::cg_exit_reason::CONVERGED ? "" : " (NOT CONVERGED)") << std::endl;
