@@ -216,3 +216,45 @@ def obstacle_solve(N, k, max_outer=50, solver=None):
         it += 1
     err = lib().orc_obstacle_error(m.h, k, _p(alpha))
     return float(err), it, alpha
+
+
+class InterfaceSystem:
+    """The two-material interface problem of `cuthho_square -i` (cuthho_square.cpp:1625-1846) on a preprocessed cut mesh:
+    full system (cell unknowns, then face unknowns; cut cells and cut faces carry two sets) and the driver's H1 error."""
+
+    def __init__(self, mesh, degree, fun=FUN_SINSIN):
+        lib().orc_interface_assemble.restype = C.c_void_p
+        self.mesh, self.degree = mesh, degree
+        self.h = C.c_void_p(lib().orc_interface_assemble(mesh.h, degree, fun))
+        if not self.h:
+            raise RuntimeError(lib().orc_last_error().decode())
+        s = (C.c_longlong * 4)()
+        lib().orc_interface_sizes(self.h, s)
+        self.n, self.nnz, self.num_all_cells, self.num_all_faces = int(s[0]), int(s[1]), int(s[2]), int(s[3])
+        self.rowptr = np.zeros(self.n + 1, np.int64); self.col = np.zeros(self.nnz, np.int32); self.val = np.zeros(self.nnz); self.rhs = np.zeros(self.n)
+        self.cell_table = np.zeros(mesh.ncells, np.int64); self.face_table = np.zeros(mesh.nfaces, np.int64)
+        lib().orc_interface_get(self.h, _p(self.rowptr, C.c_longlong), _p(self.col, C.c_int), _p(self.val), _p(self.rhs),
+                                _p(self.cell_table, C.c_longlong), _p(self.face_table, C.c_longlong))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_interface_free(self.h); self.h = None
+
+    def matrix(self):
+        import scipy.sparse as sp
+        return sp.csr_matrix((self.val, self.col, self.rowptr), shape=(self.n, self.n))
+
+    def h1_error(self, sol):
+        sol = np.ascontiguousarray(sol, np.float64); out = C.c_double(0)
+        if lib().orc_interface_error(self.h, _p(sol), C.byref(out)):
+            raise RuntimeError(lib().orc_last_error().decode())
+        return float(np.sqrt(out.value))
+
+
+def interface_local(mesh, cell, degree):
+    """local matrix ([cell-, cell+, faces-, faces+]) and load of a cut cell of the interface problem"""
+    cbs, fbs, rbs, n = dims(degree + 1, degree)
+    lc = np.zeros(4 * n * n); rhs = np.zeros(2 * cbs)
+    if lib().orc_interface_local(mesh.h, C.c_longlong(cell), degree, _p(lc), _p(rhs)):
+        raise RuntimeError(lib().orc_last_error().decode())
+    return lc.reshape(2 * n, 2 * n).T.copy(), rhs

@@ -4,6 +4,7 @@
  * apps/cuthho/cuthho_square.cpp:883-902, apps/obstacle/obstacle.cpp:147-158 and their error norms. */
 #include "orc_cut.hpp"
 #include "orc_obstacle.hpp"
+#include "orc_interface.hpp"
 #include <chrono>
 #include <cstring>
 #include <string>
@@ -56,6 +57,7 @@ void local_ops(const MeshH& H, const Cell& cl, const Problem& P, Mat& oper, Mat&
 }
 
 struct SysH { Assembler as; const MeshH* mh; Problem P; SysH(const MeshH* h, const Problem& p) : as(h->m, p.di), mh(h), P(p) {} };
+struct IfcH { InterfaceAssembler as; const MeshH* mh; int fun; IfcH(const MeshH* h, InterfaceAssembler&& a, int f) : as(std::move(a)), mh(h), fun(f) {} };
 struct ObsH { ObstacleAssembler as; const MeshH* mh; ObsH(const MeshH* h, const std::vector<bool>& inA, DegreeInfo di) : as(h->m, inA, di), mh(h) {} };
 }  // namespace
 
@@ -327,4 +329,53 @@ void orc_cell_barycenters(void* h, double* xy) { auto& m = ((MeshH*)h)->m; for (
 extern "C" void orc_mesh_set_points(void* h, const double* xy) {
     auto& m = ((MeshH*)h)->m;
     for (size_t i = 0; i < m.points.size(); i++) m.points[i] = Pt(xy[2 * i], xy[2 * i + 1]);
+}
+
+/* ---- two-material interface problem (`cuthho_square -i`, cuthho_square.cpp:1625-1846); needs orc_cut_preprocess first ---- */
+extern "C" {
+void* orc_interface_assemble(void* h, int degree, int fun) {
+    ORC_TRY
+    auto* H = (MeshH*)h;
+    if (!H->cut_done) throw std::logic_error("orc_interface_assemble: run orc_cut_preprocess first");
+    return new IfcH(H, assemble_interface_problem(H->m, H->ls, (size_t)degree, rhs_fun(fun), sol_fun(fun)), fun);
+    ORC_CATCH(nullptr)
+}
+void orc_interface_free(void* s) { delete (IfcH*)s; }
+void orc_interface_sizes(void* s, long long out[4]) {
+    auto* S = (IfcH*)s; out[0] = S->as.LHS.n; out[1] = S->as.LHS.val.size(); out[2] = S->as.num_all_cells; out[3] = S->as.num_all_faces;
+}
+void orc_interface_get(void* s, long long* rowptr, int* col, double* val, double* rhs, long long* cell_table, long long* face_table) {
+    auto* S = (IfcH*)s; auto& A = S->as.LHS;
+    std::memcpy(rowptr, A.rowptr.data(), A.rowptr.size() * 8); std::memcpy(col, A.col.data(), A.col.size() * 4);
+    std::memcpy(val, A.val.data(), A.val.size() * 8); std::memcpy(rhs, S->as.RHS.data(), S->as.RHS.size() * 8);
+    if (cell_table) for (size_t i = 0; i < S->as.cell_table.size(); i++) cell_table[i] = S->as.cell_table[i];
+    if (face_table) for (size_t i = 0; i < S->as.face_table.size(); i++) face_table[i] = S->as.face_table[i];
+}
+/* local matrix of a CUT cell in the driver's unknown order [cell-, cell+, faces-, faces+] (2n x 2n column-major) and its load (2 cbs) */
+int orc_interface_local(void* h, long long cell, int degree, double* lc_out, double* rhs_out) {
+    ORC_TRY
+    auto* H = (MeshH*)h; const Cell& cl = H->m.cells.at(cell); DegreeInfo hdi(degree + 1, degree); InterfaceParams parms;
+    const int cbs = (int)cell_basis_size(hdi.cd), nfd = 4 * (int)face_basis_size(hdi.fd);
+    Mat lc = make_hho_laplacian_interface(H->m, cl, H->ls, hdi, parms);
+    Mat sn = make_hho_cut_stabilization(H->m, cl, hdi, IN_NEGATIVE_SIDE), sp = make_hho_cut_stabilization(H->m, cl, hdi, IN_POSITIVE_SIDE);
+    lc.add_block(0, 0, sn.block(0, 0, cbs, cbs)); lc.add_block(0, 2 * cbs, sn.block(0, cbs, cbs, nfd));
+    lc.add_block(2 * cbs, 0, sn.block(cbs, 0, nfd, cbs)); lc.add_block(2 * cbs, 2 * cbs, sn.block(cbs, cbs, nfd, nfd));
+    lc.add_block(cbs, cbs, sp.block(0, 0, cbs, cbs)); lc.add_block(cbs, 2 * cbs + nfd, sp.block(0, cbs, cbs, nfd));
+    lc.add_block(2 * cbs + nfd, cbs, sp.block(cbs, 0, nfd, cbs)); lc.add_block(2 * cbs + nfd, 2 * cbs + nfd, sp.block(cbs, cbs, nfd, nfd));
+    std::memcpy(lc_out, lc.a.data(), lc.a.size() * 8);
+    if (rhs_out) {
+        Vec fn = make_rhs_where(H->m, cl, hdi.cd, IN_NEGATIVE_SIDE, rhs_fun(0)), fp = make_rhs_where(H->m, cl, hdi.cd, IN_POSITIVE_SIDE, rhs_fun(0));
+        std::memcpy(rhs_out, fn.data(), cbs * 8); std::memcpy(rhs_out + cbs, fp.data(), cbs * 8);
+    }
+    return 0;
+    ORC_CATCH(1)
+}
+/* cuthho_square.cpp:1769-1837: H1 error^2 of the cell unknowns, both parts of the cut cells */
+int orc_interface_error(void* s, const double* sol, double* h1_sq) {
+    ORC_TRY
+    auto* S = (IfcH*)s; Vec solv(sol, sol + S->as.system_size); const int fun = S->fun;
+    *h1_sq = interface_h1_error_sq(S->mh->m, S->as, solv, [fun](Pt p, double g[2]) { sol_grad(fun, p, g); });
+    return 0;
+    ORC_CATCH(1)
+}
 }

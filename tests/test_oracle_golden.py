@@ -36,6 +36,26 @@ def test_cuthho_fictdom_table(golden, k, N, r):
     assert abs(err - ref) / ref < TOL
 
 
+@pytest.mark.parametrize("k,N,r", [(k, N, 4) for k in (0, 1, 2) for N in (10, 20, 40)] + [(1, 10, 5), (2, 10, 6), (1, 20, 7)])
+def test_cuthho_interface_table(golden, k, N, r):
+    """`cuthho_square -i` (two-material interface problem; oracle/orc_interface.hpp): the "Interface" block of
+    cuthho.xlsx.  The driver solves with CG; a direct solve of the same system gives the same 6 digits.  1e-5: the k=2 column
+    of the table was produced with CG at the default 1e-9 tolerance and carries one digit less."""
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=r)
+    S = orc.InterfaceSystem(m, k)
+    A = S.matrix()
+    assert abs(A - A.T).max() < 1e-10 * abs(A).max()
+    # doubled unknowns: two sets on every cut cell and cut face (cuthho_square.cpp:1143-1161)
+    info = m.cut_info()
+    ncut_cells = int((info["cell_loc"] == 2).sum()); ncut_faces = int((info["face_loc"] == 2).sum())
+    assert S.num_all_cells == m.ncells + ncut_cells and S.num_all_faces == m.nfaces + ncut_faces
+    sol = spla.splu(A.tocsc()).solve(S.rhs)
+    err = S.h1_error(sol)
+    ref = golden["cuthho_interface"][f"k{k}_N{N}_r{r}"]
+    assert abs(err - ref) / ref < 1e-5, (err, ref)
+
+
 def test_config1_anchor():
     """BASELINE config 1: cuthho_square -f -M 32 -N 32 -k 1 (survey-derived anchor)."""
     err, S, m = _fictdom(32, 1, 4)
