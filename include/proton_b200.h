@@ -28,7 +28,7 @@ typedef enum { PB_QUAD_TENSOR_GAUSS = 0, PB_QUAD_POLY_DUNAVANT = 1 } pb_quad_kin
 typedef enum { PB_STAB_NAIVE = 0, PB_STAB_FANCY = 1, PB_STAB_CUT = 2 } pb_stab_kind;
 /* plain HHO Poisson (apps/convergence_test, apps/obstacle) or fictitious-domain cutHHO
  * (run_cuthho_fictdom, apps/cuthho/cuthho_square.cpp:806-1080) */
-typedef enum { PB_PROBLEM_HHO = 0, PB_PROBLEM_FICTDOM = 1 } pb_problem_kind;
+typedef enum { PB_PROBLEM_HHO = 0, PB_PROBLEM_FICTDOM = 1, PB_PROBLEM_INTERFACE = 2 } pb_problem_kind;
 /* the point-wise host lambdas of the drivers, as device functors: rhs_fun / sol_fun / sol_grad of
  * convergence_test.cpp:100-113 and cuthho_square.cpp:847-866 (SINSIN), obstacle.cpp:65-89 (OBSTACLE), the
  * commented-out tanh problem of convergence_test.cpp:115-138 (TANH) */
@@ -159,6 +159,20 @@ pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsigned char id[
 /* back-substitution on a strip: cell dofs of the OWNED cell rows only ([row_begin,row_end) x Nx x cbs) and the owned
  * face dofs */
 pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
+
+/* ---- two-material interface problem, `cuthho_square -i` (PB_PROBLEM_INTERFACE).  pb_assemble replaces the
+ * loop of run_cuthho_interface (apps/cuthho/cuthho_square.cpp:1667-1716): make_hho_laplacian + make_hho_naive_stabilization
+ * on uncut cells, make_hho_laplacian_interface (:390-502) + make_hho_cut_stabilization on both sides (:1689-1706) + make_rhs
+ * on both sides on cut cells, then interface_assembler::assemble / assemble_cut / finalize (:1197-1340, 1430-1434) onto the
+ * condensed face system in interface_assembler's numbering: unknown (f, a) = face_table[f]*fbs + a, the second set of a cut
+ * face fbs further (:1161-1175, 1301).  Whole-mesh contexts, HHO(k+1,k), k <= 2, kappa_1 = kappa_2 = 1 (params<T>, :293-299).
+ * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems; back-substitution and the driver's H1 error
+ * are not built yet.  pb_interface_get_local: per-cut-cell arrays in ascending cell order (what = 0: condensed block,
+ * (8 fbs)^2 column-major in the driver's local order [faces-, faces+]; 1: condensed rhs; with keep_local 2: the local matrix
+ * (2 cbs + 8 fbs)^2 in the order [cell-, cell+, faces-, faces+]; 3: the local load, 2 cbs).  pb_interface_face_table:
+ * face_table per face, -1 for Dirichlet faces. ---- */
+pb_status pb_interface_get_local(pb_ctx* ctx, int what, double* out);
+pb_status pb_interface_face_table(pb_ctx* ctx, long long* table);
 
 /* ---- driver outputs.
  * pb_pcg_history(capacity > 0): the following pb_pcg calls record nr/nr0 exactly where conjugated_gradient writes a line

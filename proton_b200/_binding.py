@@ -18,7 +18,7 @@ class PB:
     OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_UNSUPPORTED = range(5)
     QUAD_TENSOR_GAUSS, QUAD_POLY_DUNAVANT = 0, 1
     STAB_NAIVE, STAB_FANCY, STAB_CUT = 0, 1, 2
-    PROBLEM_HHO, PROBLEM_FICTDOM = 0, 1
+    PROBLEM_HHO, PROBLEM_FICTDOM, PROBLEM_INTERFACE = 0, 1, 2
     FUN_SINSIN, FUN_OBSTACLE, FUN_TANH = 0, 1, 2
     IN_NEGATIVE_SIDE, IN_POSITIVE_SIDE, ON_INTERFACE, UNDEF = 0, 1, 2, 3
     CG_CONVERGED, CG_DIVERGED, CG_MAX_ITER_REACHED = 0, 1, 2
@@ -68,6 +68,8 @@ def lib():
         L.pb_get_local.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
         L.pb_assemble_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pb_pipeline_sync.argtypes = [C.c_void_p]
+        L.pb_interface_get_local.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pb_interface_face_table.argtypes = [C.c_void_p, C.c_void_p]
         L.pb_pcg_history.argtypes = [C.c_void_p, C.c_longlong]
         L.pb_pcg_get_history.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
         L.pb_sample_solution.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
@@ -271,6 +273,22 @@ class Context:
         r = _CgResult()
         self._ck(lib().pb_pcg(self._h, C.byref(p), C.byref(r)))
         return dict(iterations=r.iterations, relative_residual=r.relative_residual, exit_reason=r.exit_reason, seconds=r.seconds)
+
+    # ---- interface problem
+    def interface_local(self, what):
+        """per-cut-cell arrays of the interface problem, ascending cell order (see pb_interface_get_local); matrices are
+        returned as [cell, row, col]"""
+        h = self.hdi; nf = 4 * h.fbs; n2 = 2 * h.cbs + 2 * nf
+        shape = {0: (2 * nf, 2 * nf), 1: (2 * nf,), 2: (n2, n2), 3: (2 * h.cbs,)}[what]
+        ncut = self.cut_counts()[0]
+        out = np.zeros((ncut,) + shape)
+        self._ck(lib().pb_interface_get_local(self._h, what, _ptr(out)))
+        return out.transpose(0, 2, 1).copy() if len(shape) == 2 else out
+
+    def interface_face_table(self):
+        t = np.zeros(self.nfaces, np.int64)
+        self._ck(lib().pb_interface_face_table(self._h, _ptr(t)))
+        return t
 
     # ---- driver outputs (SURVEY 8f.5)
     def pcg_history(self, capacity):

@@ -1,6 +1,8 @@
 // C ABI of proton_b200 (include/proton_b200.h): context, mesh, dispatch of the hand-written sm_100a kernels.
 #include <cuda_runtime.h>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_reduce.cuh>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -12,6 +14,7 @@
 
 #include "pb_local.cuh"
 #include "pb_cut.cuh"
+#include "pb_interface.cuh"
 #include "pb_norms.cuh"
 #include "pb_pcg.cuh"
 #include "pb_system.cuh"
@@ -46,6 +49,9 @@ struct pb_ctx {
     long long nrows_blk = 0, nrows = 0, nnz = 0;
     BlockRow* brows = nullptr; long long* brp = nullptr;
     long long* rowptr = nullptr; int* col = nullptr; double *val = nullptr, *rhs = nullptr;
+    // interface problem (pb_api_interface.inl): per-cut-cell blocks, face_table, general-CSR flag
+    double *Sx = nullptr, *gx = nullptr, *recAx = nullptr, *recbx = nullptr, *lcx = nullptr, *fx = nullptr;
+    int* ftab = nullptr; bool general_csr = false;
     // solver
     double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *iAb = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
@@ -150,6 +156,7 @@ extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
 
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
+    dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); c->general_csr = false;
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
     dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->iAb); dfree(&c->parts); dfree(&c->scal);
     dfree(&c->ob_alpha); dfree(&c->ob_beta); dfree(&c->ob_gamma); dfree(&c->ob_xprev); dfree(&c->ob_inA); c->ob_ready = false;
@@ -253,6 +260,7 @@ extern "C" pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table) {
     return PB_OK;
 }
 #include "pb_api_cut.inl"
+#include "pb_api_interface.inl"
 
 // ------------------------------------------------------------------------------------------------ stage 1+2
 template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB>
@@ -408,11 +416,18 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
         bool c1 = fd > 0 && (cd == fd - 1 || cd == fd || cd == fd + 1), c2 = fd == 0 && (cd == fd || cd == fd + 1);
         if (!(c1 || c2)) cd = fd;
     }
-    NEED(p->problem == PB_PROBLEM_HHO || p->problem == PB_PROBLEM_FICTDOM, PB_ERR_INVALID, "pb_assemble: bad problem kind");
+    NEED(p->problem == PB_PROBLEM_HHO || p->problem == PB_PROBLEM_FICTDOM || p->problem == PB_PROBLEM_INTERFACE, PB_ERR_INVALID, "pb_assemble: bad problem kind");
+    const bool ifc = p->problem == PB_PROBLEM_INTERFACE;
+    if (ifc) {
+        NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: the interface problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");
+        NEED(ctx->quad_kind == PB_QUAD_POLY_DUNAVANT, PB_ERR_INVALID, "pb_assemble: the interface problem runs on the cuthho_poly mesh (PB_QUAD_POLY_DUNAVANT)");
+        NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_assemble: the interface problem is built for whole-mesh contexts");
+        NEED(p->stab_kind != PB_STAB_FANCY, PB_ERR_INVALID, "pb_assemble: the interface driver uses the naive / cut stabilisation");
+    }
     if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");
     int sk = p->stab_kind == PB_STAB_FANCY ? 1 : 0;
     const int rqd = 2 * (cd + p->rhs_degree_increase);
-    bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc);
+    bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc) || ctx->general_csr != ifc;
     ctx->prm = *p; ctx->CD = cd; ctx->FD = fd;
     ctx->C = cell_basis_size(cd); ctx->F = fd + 1; ctx->R = cell_basis_size(fd + 1); ctx->NF = 4 * ctx->F; ctx->N = ctx->C + ctx->NF;
     const long long nc = ctx->ncells_local;
@@ -424,11 +439,12 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
             CK(dalloc(ctx, &ctx->lc, (size_t)nc * ctx->N * ctx->N)); CK(dalloc(ctx, &ctx->oper, (size_t)nc * ctx->N * ctx->R));
             CK(dalloc(ctx, &ctx->rhsloc, (size_t)nc * ctx->C));
         }
-        pb_status st = build_structure(ctx); if (st != PB_OK) return st;
+        if (!ifc) { pb_status st = build_structure(ctx); if (st != PB_OK) return st; }
+        ctx->general_csr = ifc;
     }
     LocalArgs A{};
     A.grid = ctx->grid; A.grid.row_begin = ctx->strip.cell_row0;      // local cell 0 sits in row cell_row0
-    A.points = ctx->points; A.cell_loc = p->problem == PB_PROBLEM_FICTDOM ? ctx->cell_loc_g + ctx->strip.cell_row0 * ctx->grid.Nx : nullptr;
+    A.points = ctx->points; A.cell_loc = (p->problem == PB_PROBLEM_FICTDOM || ifc) ? ctx->cell_loc_g + ctx->strip.cell_row0 * ctx->grid.Nx : nullptr;
     A.ncells = nc; A.fun = p->fun; A.problem = p->problem; A.eta = p->eta;
     A.S = ctx->S; A.g = ctx->g; A.recA = ctx->recA; A.recb = ctx->recb;
     A.lc = p->keep_local ? ctx->lc : nullptr; A.oper = p->keep_local ? ctx->oper : nullptr; A.rhs = p->keep_local ? ctx->rhsloc : nullptr;
@@ -449,9 +465,13 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     if (p->problem == PB_PROBLEM_FICTDOM && ctx->ncut > 0) {
         pb_status st = launch_cut(ctx, A, cd, fd); if (st != PB_OK) return st;
     }
+    if (ifc) { pb_status st = launch_interface_cut(ctx, p, cd, fd); if (st != PB_OK) return st; }
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     if (ctx->out_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_out, 0));         // previous rhs read-back done before K3 overwrites rhs
-    { pb_status st = scatter_system(ctx); if (st != PB_OK) return st; }
+    if (ifc) {
+        if (ctx->out_pending) { CK(cudaStreamSynchronize(ctx->s_out)); ctx->out_pending = false; }   // the system arrays are reallocated below
+        pb_status st = build_interface_system(ctx); if (st != PB_OK) return st;
+    } else { pb_status st = scatter_system(ctx); if (st != PB_OK) return st; }
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     if (host_rhs) {
         if (!ctx->s_out) { CK(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming)); }

@@ -120,7 +120,8 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     NEED(whole || (ctx->world > 1 && ctx->comm), PB_ERR_STATE, "pb_pcg: this context owns a strip: call pb_dist_init on every rank first");
     CK(cudaSetDevice(ctx->device));
     const long long n = ctx->nrows; const int F = ctx->F;
-    const long long xoff = ctx->strip.col_lo * F, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F, nfull = (ctx->strip.col_hi - ctx->strip.col_lo) * F;
+    const long long xoff = ctx->strip.col_lo * F, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F;
+    const long long nfull = ctx->general_csr ? n : (ctx->strip.col_hi - ctx->strip.col_lo) * F;      // interface problem: whole mesh, its own numbering
     if (!ctx->x) {
         CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
         CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
@@ -142,7 +143,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     if (blockpre && !ctx->iAb) CK(dalloc(ctx, &ctx->iAb, (size_t)n * F));
     const long long nbr_own = n / F;
     const int lpr = spmv_lanes(F);
-    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1;   // scalar CSR: comparison runs, and F = 1 where a
+    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || ctx->general_csr;   // scalar CSR: comparison runs, and F = 1 where a
                                                                                // 64-byte face record per row costs more than 7 column indices
     int nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
     if (!use_csr) {
@@ -282,6 +283,7 @@ static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** kee
 extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && cell_dofs, PB_ERR_STATE, "pb_recover_strip: no face solution");
+    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_recover: not built for the interface problem yet");
     CK(cudaSetDevice(ctx->device));
     pb_status st = recover_owned(ctx, cell_dofs); if (st != PB_OK) return st;
     if (face_dofs) CK(cudaMemcpy(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
@@ -311,7 +313,7 @@ static cudaError_t launch_norms_t(pb_ctx* c, NormArgs& A, int grid) {
 extern "C" pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && n_points, PB_ERR_STATE, "pb_sample_solution: no face solution");
-    NEED(ctx->prm.problem == PB_PROBLEM_HHO, PB_ERR_UNSUPPORTED, "pb_sample_solution: uncut HHO problems only");
+    NEED(ctx->prm.problem == PB_PROBLEM_HHO && !ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_sample_solution: uncut HHO problems only");
     CK(cudaSetDevice(ctx->device));
     const int cd = ctx->CD, qk = ctx->quad_kind;
     NEED(cd >= 0 && cd <= 4, PB_ERR_UNSUPPORTED, "pb_sample_solution: cell degree > 4");
@@ -342,6 +344,7 @@ extern "C" pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capa
 extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && out, PB_ERR_STATE, "pb_error_norms: no face solution");
+    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_error_norms: not built for the interface problem yet");
     CK(cudaSetDevice(ctx->device));
     double *uc = nullptr, *xfull = nullptr;
     pb_status st = recover_owned(ctx, nullptr, &uc, &xfull); if (st != PB_OK) return st;

@@ -1,0 +1,102 @@
+"""GPU parity of the two-material interface problem (`cuthho_square -i`) against oracle/orc_interface.hpp,
+which is pinned against the reference's "Interface" table (tests/test_oracle_golden.py):
+  * local matrices and loads of the cut cells (make_hho_laplacian_interface + both cut stabilisations), 1e-11;
+  * face_table (doubled cut faces) bit-exact, sizes of the condensed system;
+  * condensed CSR (pattern bit-exact, values 1e-10) and rhs against the Schur complement of the oracle's full system;
+  * PCG solution of the condensed system against the oracle's direct solve (face part), 1e-8."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+pytestmark = pytest.mark.gpu
+
+import proton_b200 as pb
+from proton_b200 import PB
+from oracle import orc
+
+
+def frob_rel(a, b):
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pb.Context(0)
+    yield c
+    c.close()
+
+
+def _setup(ctx, N, k, r=4, keep_local=False):
+    m = orc.Mesh(N, poly=True)
+    m.cut_preprocess(refsteps=r)
+    ctx.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT)
+    ctx.cut_levelset(0, 0.35, 0.5, 0.5)
+    ctx.cut_preprocess(r)
+    ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE, keep_local=keep_local)
+    return m
+
+
+@pytest.mark.parametrize("k,N", [(0, 10), (1, 10), (2, 10), (2, 17)])
+def test_interface_cut_cell_local_matrices(ctx, k, N):
+    m = _setup(ctx, N, k, keep_local=True)
+    cut = np.flatnonzero(m.cut_info()["cell_loc"] == 2)
+    lc = ctx.interface_local(2); f = ctx.interface_local(3)
+    assert len(cut) == len(lc) > 0
+    worst = wf = 0.0
+    for s, c in enumerate(cut):
+        ref, fref = orc.interface_local(m, int(c), k)
+        worst = max(worst, frob_rel(lc[s], ref)); wf = max(wf, frob_rel(f[s], fref))
+    assert worst < 1e-11 and wf < 1e-12, (worst, wf)
+
+
+@pytest.mark.parametrize("k,N", [(0, 10), (1, 12), (2, 10), (2, 20)])
+def test_interface_condensed_system_and_solve(ctx, k, N):
+    m = _setup(ctx, N, k)
+    S = orc.InterfaceSystem(m, k)
+    F = k + 1; cbs = (k + 2) * (k + 3) // 2
+    # numbering: face_table bit-exact (Dirichlet faces are -1 here, unused there)
+    ft = ctx.interface_face_table()
+    dirichlet = m.faces()[1].astype(bool)
+    assert np.array_equal(ft[~dirichlet], S.face_table[~dirichlet]) and np.all(ft[dirichlet] == -1)
+    nT = cbs * S.num_all_cells
+    assert ctx.n_rows == S.n - nT
+    # condensed system = Schur complement of the oracle's full system on the cell unknowns
+    K = S.matrix().tocsc()
+    KTT, KTF, KFT, KFF = K[:nT, :nT], K[:nT, nT:], K[nT:, :nT], K[nT:, nT:]
+    lu = spla.splu(KTT)
+    Sc = KFF - KFT @ sp.csc_matrix(lu.solve(KTF.toarray()))
+    bc = S.rhs[nT:] - KFT @ lu.solve(S.rhs[:nT])
+    rp, col, val, rhs = ctx.csr()
+    A = sp.csr_matrix((val, col, rp), shape=(ctx.n_rows, ctx.n_rows))
+    Sd = Sc.toarray(); Ad = A.toarray()
+    assert np.max(np.abs(Ad - Sd)) < 1e-10 * np.max(np.abs(Sd))
+    # pattern: union of the local cliques with explicit zeros kept (as the reference's triplets)
+    stored = np.zeros_like(Ad, dtype=bool); stored[np.repeat(np.arange(ctx.n_rows), np.diff(rp)), col] = True
+    assert np.all(np.abs(Sd[~stored]) < 1e-9 * np.max(np.abs(Sd)))      # nothing of the Schur complement falls outside the pattern
+    assert all(np.all(np.diff(col[rp[i]:rp[i + 1]]) > 0) for i in range(ctx.n_rows))        # sorted, no duplicates
+    assert frob_rel(rhs, bc) < 1e-10
+    # solve: the reference's CG settings of the driver (diagonal preconditioner), against the direct solve
+    sol = spla.splu(K).solve(S.rhs)
+    res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, True))
+    assert res["exit_reason"] == PB.CG_CONVERGED
+    x = ctx.face_solution()
+    assert frob_rel(x, sol[nT:]) < 1e-8
+    # the oracle's H1 error with the GPU face solution back-substituted through the oracle's cell rows
+    full = np.concatenate([lu.solve(S.rhs[:nT] - KTF @ x), x])
+    assert abs(S.h1_error(full) - S.h1_error(sol)) < 1e-8 * S.h1_error(sol)
+
+
+def test_interface_golden_through_the_gpu_system(ctx, golden):
+    """reference table value (cuthho.xlsx, Interface block) from the GPU-assembled and GPU-solved condensed system"""
+    k, N = 1, 20
+    m = _setup(ctx, N, k)
+    S = orc.InterfaceSystem(m, k)
+    cbs = (k + 2) * (k + 3) // 2; nT = cbs * S.num_all_cells
+    K = S.matrix().tocsc()
+    res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, True))
+    assert res["exit_reason"] == PB.CG_CONVERGED
+    x = ctx.face_solution()
+    full = np.concatenate([spla.splu(K[:nT, :nT]).solve(S.rhs[:nT] - K[:nT, nT:] @ x), x])
+    ref = golden["cuthho_interface"][f"k{k}_N{N}_r4"]
+    assert abs(S.h1_error(full) - ref) / ref < 1e-5
