@@ -221,7 +221,7 @@ class Context:
     def assemble(self, hdi, stab_kind=PB.STAB_FANCY, problem=PB.PROBLEM_HHO, fun=PB.FUN_SINSIN, rhs_degree_increase=0, eta=5.0, keep_local=False):
         p = _AssemblyParams(hdi.cd, hdi.fd, stab_kind, problem, fun, rhs_degree_increase, eta, int(keep_local))
         self._ck(lib().pb_assemble(self._h, C.byref(p)))
-        self.hdi = hdi
+        self.hdi = hdi; self.problem = problem
         n = C.c_longlong(); nnz = C.c_longlong(); nc = C.c_longlong(); nl = C.c_longlong()
         self._ck(lib().pb_system_sizes(self._h, C.byref(n), C.byref(nnz), C.byref(nc), C.byref(nl)))
         self.n_rows, self.nnz, self.ncells_local, self.n_local = n.value, nnz.value, nc.value, nl.value
@@ -319,7 +319,8 @@ class Context:
         self._ck(lib().pb_set_face_solution(self._h, _ptr(x)))
 
     def recover(self):
-        full = np.zeros(self.ncells * self.hdi.cbs + self.n_rows); self._ck(lib().pb_recover(self._h, _ptr(full))); return full
+        ncell_sets = self.ncells + (self.cut_counts()[0] if getattr(self, "problem", 0) == PB.PROBLEM_INTERFACE else 0)   # cut cells carry two sets
+        full = np.zeros(ncell_sets * self.hdi.cbs + self.n_rows); self._ck(lib().pb_recover(self._h, _ptr(full))); return full
 
     def error_norms(self):
         out = np.zeros(3); self._ck(lib().pb_error_norms(self._h, _ptr(out))); return out

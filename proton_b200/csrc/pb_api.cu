@@ -628,7 +628,10 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
     }
 }
 
+static pb_status interface_recover(pb_ctx* ctx, double* full);
+static pb_status interface_error(pb_ctx* ctx, double out[3]);
 #include "pb_api_dist.inl"
+#include "pb_api_interface_post.inl"
 #include "pb_api_obstacle.inl"
 
 extern "C" pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg) {

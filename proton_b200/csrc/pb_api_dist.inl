@@ -283,7 +283,7 @@ static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** kee
 extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && cell_dofs, PB_ERR_STATE, "pb_recover_strip: no face solution");
-    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_recover: not built for the interface problem yet");
+    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_recover_strip: whole-mesh pb_recover only for the interface problem");
     CK(cudaSetDevice(ctx->device));
     pb_status st = recover_owned(ctx, cell_dofs); if (st != PB_OK) return st;
     if (face_dofs) CK(cudaMemcpy(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
@@ -294,6 +294,7 @@ extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* fa
 extern "C" pb_status pb_recover(pb_ctx* ctx, double* full) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && full, PB_ERR_STATE, "pb_recover: no face solution");
+    if (ctx->general_csr) { CK(cudaSetDevice(ctx->device)); return interface_recover(ctx, full); }
     NEED(ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_recover: whole-mesh contexts only (strips: pb_recover_strip)");
     return pb_recover_strip(ctx, full, full + ctx->ncells_global * ctx->C);
 }
@@ -344,7 +345,7 @@ extern "C" pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capa
 extern "C" pb_status pb_error_norms(pb_ctx* ctx, double out[3]) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && out, PB_ERR_STATE, "pb_error_norms: no face solution");
-    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_error_norms: not built for the interface problem yet");
+    if (ctx->general_csr) { CK(cudaSetDevice(ctx->device)); return interface_error(ctx, out); }
     CK(cudaSetDevice(ctx->device));
     double *uc = nullptr, *xfull = nullptr;
     pb_status st = recover_owned(ctx, nullptr, &uc, &xfull); if (st != PB_OK) return st;

@@ -1,0 +1,183 @@
+// C ABI — interface problem, after the solve: back-substitution in the layout of the reference's solution vector
+// (cell unknowns with cell_table, cut cells twice: negative then positive part, cuthho_square.cpp:1143-1151, 1343-1365;
+// then the face unknowns) and the driver's H1 error (run_cuthho_interface, :1769-1837).
+
+__global__ void ifc_gather_regular_kernel(Grid g, int F, const int* __restrict__ ftab, const double* __restrict__ x, double* __restrict__ xreg) {
+    const long long nc = g.Nx * g.Ny;
+    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < nc; c += (long long)gridDim.x * blockDim.x) {
+        const long long ci = c % g.Nx, cj = c / g.Nx;
+        long long f[4]; cell_faces(g, ci, cj, f);
+        for (int li = 0; li < 4; li++) {
+            if (cell_face_dirichlet(g, ci, cj, li)) continue;
+            const long long cf = cell_face_compressed(g, ci, cj, li);
+            for (int a = 0; a < F; a++) xreg[cf * F + a] = x[(long long)ftab[f[li]] * F + a];     // first set (both cells write the same value)
+        }
+    }
+}
+__global__ void ifc_recover_cut_kernel(Grid g, int F, int C, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ face_loc,
+                                       const int* __restrict__ ftab, const double* __restrict__ recAx, const double* __restrict__ recbx,
+                                       const double* __restrict__ x, double* __restrict__ ucut) {
+    const int C2 = 2 * C, NF2 = 8 * F;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)ncut * C2; t += (long long)gridDim.x * blockDim.x) {
+        const long long slot = t / C2; const int a = (int)(t - slot * C2);
+        const long long c = cut_cells[slot], ci = c % g.Nx, cj = c / g.Nx;
+        long long f[4]; cell_faces(g, ci, cj, f);
+        double v = recbx[t];
+        for (int col = 0; col < NF2; col++) v -= recAx[slot * (long long)(NF2 * C2) + a + col * C2] * x[ifc_slot_dof(g, F, face_loc, ftab, f, col)];
+        ucut[t] = v;
+    }
+}
+__global__ void ifc_pack_cells_kernel(Grid g, int C, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ cell_loc,
+                                      const double* __restrict__ uc, const double* __restrict__ ucut, double* __restrict__ out) {
+    const long long nc = g.Nx * g.Ny;
+    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < nc; c += (long long)gridDim.x * blockDim.x) {
+        int lo = 0, hi = ncut;                      // cut cells before c = cell_table[c] - c
+        while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
+        double* o = out + (c + lo) * C;
+        if (cell_loc[c] == PB_ON_INTERFACE) for (int a = 0; a < 2 * C; a++) o[a] = ucut[(long long)lo * 2 * C + a];
+        else for (int a = 0; a < C; a++) o[a] = uc[c * C + a];
+    }
+}
+
+// H1 error^2 of the cell unknowns: uncut cells over integrate(msh, cl, 2 cd), cut cells over both parts.  One warp per
+// cell, lane 0 accumulates in cell order: deterministic.
+template <int CD>
+__global__ void __launch_bounds__(32) interface_h1_kernel(Grid g, const double2* __restrict__ points, const int* __restrict__ node_loc,
+                                                           const int* __restrict__ cell_loc, const int* __restrict__ cut_cells, const double2* __restrict__ iface,
+                                                           int ncut, int NI, int fun, const double* __restrict__ uc, const double* __restrict__ ucut,
+                                                           double* __restrict__ parts) {
+    constexpr int C = cell_basis_size(CD);
+    __shared__ double tp[2 * CUT_MAX_TP];
+    __shared__ int s_ntp;
+    const int lane = threadIdx.x;
+    const long long nc = g.Nx * g.Ny;
+    double sum = 0.0;
+    for (long long c = blockIdx.x; c < nc; c += gridDim.x) {
+        const long long ci = c % g.Nx, cj = c / g.Nx, p0 = grid_point(g, ci, cj);
+        const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
+        CellGeom geo; int nloc[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const double2 v = points[pid[i]]; geo.vx[i] = v.x; geo.vy[i] = v.y; nloc[i] = node_loc[pid[i]]; }
+        cell_geometry(geo);
+        const double ih = geo.ihalf;
+        double acc = 0.0;
+        auto point_term = [&](const double* u, double x, double y, double w) {
+            double phi[C], dx[C], dy[C];
+            eval_cell_basis<CD>((x - geo.barx) * ih, (y - geo.bary) * ih, ih, phi, dx, dy);
+            double gx = 0, gy = 0;
+#pragma unroll
+            for (int i = 1; i < C; i++) { gx += u[i] * dx[i]; gy += u[i] * dy[i]; }
+            double rgx, rgy; fun_grad(fun, x, y, rgx, rgy);
+            acc += w * ((rgx - gx) * (rgx - gx) + (rgy - gy) * (rgy - gy));
+        };
+        if (cell_loc[c] != PB_ON_INTERFACE) {
+            constexpr int nq = cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * CD);
+            for (int q = lane; q < nq; q += 32) { double x, y, w; cell_qp<PB_QUAD_POLY_DUNAVANT, 2 * CD>(geo, q, x, y, w); point_term(uc + c * C, x, y, w); }
+        } else {
+            int lo = 0, hi = ncut - 1;
+            while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
+            const double2* I = iface + (long long)lo * NI;
+            for (int sd = 0; sd < 2; sd++) {
+                const int WHERE = sd == 0 ? PB_IN_NEGATIVE_SIDE : PB_IN_POSITIVE_SIDE;
+                __syncwarp();
+                if (lane == 0) {
+                    int n = 0;
+                    auto push = [&](double x, double y) { tp[2 * n] = x; tp[2 * n + 1] = y; n++; };
+                    auto push_iface = [&]() {
+                        if (sd == 0) for (int i = 0; i < NI; i++) push(I[i].x, I[i].y);
+                        else for (int i = NI - 1; i >= 0; i--) push(I[i].x, I[i].y);
+                    };
+                    const bool c1 = nloc[0] == WHERE && nloc[3] != WHERE, c2 = nloc[0] != WHERE && nloc[3] == WHERE, c3 = nloc[0] != WHERE && nloc[3] != WHERE;
+                    if (c1 || c2 || c3) { for (int i = 0; i < 4; i++) if (nloc[i] == WHERE) push(sel4(geo.vx, i), sel4(geo.vy, i)); push_iface(); }
+                    else {
+                        int i = 0;
+                        while (i < 4 && nloc[i] == WHERE) { push(sel4(geo.vx, i), sel4(geo.vy, i)); i++; }
+                        push_iface();
+                        while (i < 4 && nloc[i] != WHERE) i++;
+                        while (i < 4 && nloc[i] == WHERE) { push(sel4(geo.vx, i), sel4(geo.vy, i)); i++; }
+                    }
+                    s_ntp = n;
+                }
+                __syncwarp();
+                const int ntp = s_ntp;
+                double rx = 0, ry = 0, den = 0; const double x0 = tp[0], y0 = tp[1];
+                for (int i = 2; i < ntp; i++) {
+                    const double ax = tp[2 * (i - 1)] - x0, ay = tp[2 * (i - 1) + 1] - y0, bx = tp[2 * i] - x0, by = tp[2 * i + 1] - y0;
+                    const double d = (ax * by - ay * bx) / 2.0; rx += (ax + bx) * d; ry += (ay + by) * d; den += d;
+                }
+                const double pbx = x0 + rx / (den * 3), pby = y0 + ry / (den * 3);
+                const int ri = dunavant_rule_index(2 * CD), np = c_qt.dun_n[ri], nq = ntp * np;
+                for (int q = lane; q < nq; q += 32) {
+                    const int t = q / np, p = q - t * np, t1 = (t + 1) % ntp;
+                    const double ax = tp[2 * t], ay = tp[2 * t + 1], bx = tp[2 * t1], by = tp[2 * t1 + 1];
+                    const double area = fabs(((ax - pbx) * (by - pby) - (ay - pby) * (bx - pbx)) / 2.0);
+                    const double* row = c_qt.dun[ri][p];
+                    point_term(ucut + (long long)lo * 2 * C + sd * C, pbx * row[0] + ax * row[1] + bx * row[2], pby * row[0] + ay * row[1] + by * row[2], area * row[3]);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        sum += acc;
+        __syncwarp();
+    }
+    if (lane == 0) parts[blockIdx.x] = sum;
+}
+
+// cell unknowns of all cells (uc: regular cell order; ucut: [u-, u+] per cut slot) from the face solution ctx->x
+static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** ucut_out) {
+    const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;
+    const long long nc = g.Nx * g.Ny, nreg = num_free_faces(g) * F;
+    double *xreg = nullptr, *uc = nullptr, *ucut = nullptr;
+    CK(cudaMalloc((void**)&xreg, (size_t)nreg * 8)); CK(cudaMalloc((void**)&uc, (size_t)nc * C * 8));
+    CK(cudaMalloc((void**)&ucut, (size_t)(ctx->ncut > 0 ? ctx->ncut : 1) * 2 * C * 8));
+    ifc_gather_regular_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, F, ctx->ftab, ctx->x, xreg);
+#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, 0, nc, 0, C, ctx->prm.fun, ctx->points, ctx->recA, ctx->recb, xreg, 0, uc)
+    switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; default: PB_REC(2); break; }
+#undef PB_REC
+    if (ctx->ncut > 0)
+        ifc_recover_cut_kernel<<<148 * 2, 256, 0, ctx->stream>>>(g, F, C, ctx->ncut, ctx->cut_cells, ctx->face_loc, ctx->ftab, ctx->recAx, ctx->recbx, ctx->x, ucut);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(xreg);
+    if (e != cudaSuccess) { cudaFree(uc); cudaFree(ucut); return fail(ctx, PB_ERR_CUDA, "interface back-substitution failed: %s", cudaGetErrorString(e)); }
+    *uc_out = uc; *ucut_out = ucut;
+    return PB_OK;
+}
+
+static pb_status interface_recover(pb_ctx* ctx, double* full) {
+    const Grid& g = ctx->grid; const int C = ctx->C;
+    const long long nc = g.Nx * g.Ny, ncell_dofs = (nc + ctx->ncut) * C;
+    double *uc = nullptr, *ucut = nullptr, *packed = nullptr;
+    pb_status st = interface_cell_unknowns(ctx, &uc, &ucut); if (st != PB_OK) return st;
+    CK(cudaMalloc((void**)&packed, (size_t)ncell_dofs * 8));
+    ifc_pack_cells_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, C, ctx->ncut, ctx->cut_cells, ctx->cell_loc_g, uc, ucut, packed);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(full, packed, (size_t)ncell_dofs * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(full + ncell_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(uc); cudaFree(ucut); cudaFree(packed);
+    if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_recover (interface): %s", cudaGetErrorString(e));
+    return PB_OK;
+}
+
+static pb_status interface_error(pb_ctx* ctx, double out[3]) {
+    const Grid& g = ctx->grid;
+    double *uc = nullptr, *ucut = nullptr, *parts = nullptr;
+    pb_status st = interface_cell_unknowns(ctx, &uc, &ucut); if (st != PB_OK) return st;
+    const int grid = 148 * 16;
+    CK(cudaMalloc((void**)&parts, (size_t)grid * 8));
+#define PB_H1(CD_) interface_h1_kernel<CD_><<<grid, 32, 0, ctx->stream>>>(g, ctx->points, ctx->node_loc, ctx->cell_loc_g, ctx->cut_cells, ctx->iface, ctx->ncut, ctx->NI, \
+                                                                         ctx->prm.fun, uc, ucut, parts)
+    switch (ctx->CD) { case 1: PB_H1(1); break; case 2: PB_H1(2); break; default: PB_H1(3); break; }
+#undef PB_H1
+    std::vector<double> h((size_t)grid);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h.data(), parts, h.size() * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(uc); cudaFree(ucut); cudaFree(parts);
+    if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_error_norms (interface): %s", cudaGetErrorString(e));
+    out[0] = out[1] = out[2] = 0.0;
+    for (double v : h) out[0] += v;
+    return PB_OK;
+}

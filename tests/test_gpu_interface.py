@@ -82,21 +82,25 @@ def test_interface_condensed_system_and_solve(ctx, k, N):
     assert res["exit_reason"] == PB.CG_CONVERGED
     x = ctx.face_solution()
     assert frob_rel(x, sol[nT:]) < 1e-8
-    # the oracle's H1 error with the GPU face solution back-substituted through the oracle's cell rows
-    full = np.concatenate([lu.solve(S.rhs[:nT] - KTF @ x), x])
-    assert abs(S.h1_error(full) - S.h1_error(sol)) < 1e-8 * S.h1_error(sol)
+    # back-substitution on the device, in the layout of the reference's solution vector (cell_table: cut cells twice)
+    full = ctx.recover()
+    assert full.shape == sol.shape and frob_rel(full, sol) < 1e-8
+    # the driver's H1 error: oracle on the GPU solution, and the device kernel
+    e_ref = S.h1_error(sol)
+    assert abs(S.h1_error(full) - e_ref) < 1e-8 * e_ref
+    e_dev = np.sqrt(ctx.error_norms()[0])
+    assert abs(e_dev - e_ref) < 1e-8 * e_ref, (e_dev, e_ref)
 
 
-def test_interface_golden_through_the_gpu_system(ctx, golden):
-    """reference table value (cuthho.xlsx, Interface block) from the GPU-assembled and GPU-solved condensed system"""
-    k, N = 1, 20
+@pytest.mark.parametrize("k,N", [(0, 20), (1, 20), (2, 10), (2, 40)])
+def test_interface_golden_through_the_gpu_path(ctx, golden, k, N):
+    """reference table values (cuthho.xlsx, Interface block) through the whole GPU path: assembly, PCG, back-substitution, H1 error"""
     m = _setup(ctx, N, k)
     S = orc.InterfaceSystem(m, k)
     cbs = (k + 2) * (k + 3) // 2; nT = cbs * S.num_all_cells
     K = S.matrix().tocsc()
     res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, True))
     assert res["exit_reason"] == PB.CG_CONVERGED
-    x = ctx.face_solution()
-    full = np.concatenate([spla.splu(K[:nT, :nT]).solve(S.rhs[:nT] - K[:nT, nT:] @ x), x])
     ref = golden["cuthho_interface"][f"k{k}_N{N}_r4"]
-    assert abs(S.h1_error(full) - ref) / ref < 1e-5
+    assert abs(np.sqrt(ctx.error_norms()[0]) - ref) / ref < 1e-5
+    assert abs(S.h1_error(ctx.recover()) - ref) / ref < 1e-5
