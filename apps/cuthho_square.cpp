@@ -1,6 +1,6 @@
 // cuthho_square — the reference's fictitious-domain cutHHO driver (apps/cuthho/cuthho_square.cpp:1940-2068,
 // run_cuthho_fictdom :806-1080) on the B200 path.  Same getopt interface: -k degree -M Nx -N Ny -r refine steps -f.
-// -i (two-material interface problem) is the next row of the scope table and is refused.
+// -i runs the two-material interface problem (run_cuthho_interface, :1625-1846) the same way.
 #include <unistd.h>
 
 #include <cmath>
@@ -26,7 +26,23 @@ int main(int argc, char** argv) {
         default: std::cout << "wrong arguments" << std::endl; return 1;
         }
     }
-    if (solve_interface) { std::cout << "the interface problem (-i) is not on the B200 path yet" << std::endl; return 1; }
+    if (solve_interface) {
+        try {       // run_cuthho_interface (cuthho_square.cpp:1625-1846): as in main(), the interface run comes first
+            pb::cartesian_mesh<double> msh(mip, pb::cartesian_mesh<double>::cuthho_poly);
+            pb::circle_level_set<double> level_set_function(0.35, 0.5, 0.5);
+            msh.cut_preprocess(level_set_function, (int)int_refsteps);
+            auto assembler = pb::make_assembler(msh, pb::hho_degree_info(degree + 1, degree));
+            assembler.assemble_all(PB_STAB_CUT, PB_PROBLEM_INTERFACE, PB_FUN_SINSIN, 0, 5.0);
+            std::cout << "System unknowns (condensed): " << assembler.system_size() << std::endl;
+            pb::cg_params<double> cgp; cgp.apply_preconditioner = true; cgp.convergence_threshold = 1e-13; cgp.divergence_threshold = 1e8;
+            cgp.max_iter = 20 * assembler.system_size(); cgp.histfile = "cuthho_cg_hist.dat";       // :1736-1743
+            std::vector<double> sol; size_t iters = 0;
+            auto er = pb::conjugated_gradient(assembler, sol, cgp, &iters);
+            std::cout << "CG iterations: " << iters << (er == pb::cg_exit_reason::CONVERGED ? "" : " (NOT CONVERGED)") << std::endl;
+            auto e = assembler.error_norms();
+            printf("Energy-norm absolute error:           %.10e\n", std::sqrt(e[0]));                  // :1837
+        } catch (const std::exception& ex) { std::cerr << ex.what() << std::endl; return 2; }
+    }
     if (!solve_fictdom) return 0;
     try {
         pb::cartesian_mesh<double> msh(mip, pb::cartesian_mesh<double>::cuthho_poly);

@@ -39,12 +39,22 @@ def test_obstacle_driver_prints_reference_error(golden):
 
 
 @pytest.mark.gpu
-def test_cuthho_square_driver_prints_reference_error(golden):
+def test_cuthho_square_driver_prints_reference_error(golden, tmp_path):
     _build()
-    r = subprocess.run([os.path.join(BIN, "cuthho_square"), "-f", "-k", "1", "-M", "10", "-N", "10", "-r", "4"], capture_output=True, text=True, check=True)
+    r = subprocess.run([os.path.join(BIN, "cuthho_square"), "-f", "-k", "1", "-M", "10", "-N", "10", "-r", "4"], capture_output=True, text=True, check=True, cwd=tmp_path)
     err = float(re.search(r"H1-error : ([0-9.eE+-]+)", r.stdout).group(1))
     ref = golden["cuthho_fictdom"]["k1_N10_r4"]
     assert abs(err - ref) / ref < 5e-6
+
+
+@pytest.mark.gpu
+def test_cuthho_square_interface_driver_prints_reference_error(golden, tmp_path):
+    _build()
+    r = subprocess.run([os.path.join(BIN, "cuthho_square"), "-i", "-k", "1", "-M", "20", "-N", "20", "-r", "4"], capture_output=True, text=True, check=True, cwd=tmp_path)
+    err = float(re.search(r"Energy-norm absolute error:\s+([0-9.eE+-]+)", r.stdout).group(1))
+    ref = golden["cuthho_interface"]["k1_N20_r4"]
+    assert abs(err - ref) / ref < 1e-5
+    assert (tmp_path / "cuthho_cg_hist.dat").exists()
 
 
 @pytest.mark.gpu
