@@ -3,6 +3,8 @@
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_reduce.cuh>
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -52,6 +54,9 @@ struct pb_ctx {
     // interface problem (pb_api_interface.inl): per-cut-cell blocks, face_table, general-CSR flag
     double *Sx = nullptr, *gx = nullptr, *recAx = nullptr, *recbx = nullptr, *lcx = nullptr, *fx = nullptr;
     int* ftab = nullptr; bool general_csr = false;
+    int* irr_rows = nullptr; int n_irr_rows = 0; int* irr_faces = nullptr; int n_irr_faces = 0; bool ifc_struct_ok = false;
+    unsigned long long *ifc_k0 = nullptr, *ifc_k1 = nullptr; double *ifc_v0 = nullptr, *ifc_v1 = nullptr; long long* ifc_dnum = nullptr;
+    void* ifc_tmp = nullptr; size_t ifc_tmp_bytes = 0; long long ifc_T = 0, ifc_ncut_alloc = 0;       // block rows of the cut cells' faces (scalar SpMV pass)
     // solver
     double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *iAb = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
@@ -156,7 +161,8 @@ extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
 
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
-    dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); c->general_csr = false;
+    dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); dfree(&c->irr_rows); c->n_irr_rows = 0; dfree(&c->irr_faces); c->n_irr_faces = 0; c->ifc_struct_ok = false;
+    dfree(&c->ifc_k0); dfree(&c->ifc_k1); dfree(&c->ifc_v0); dfree(&c->ifc_v1); dfree(&c->ifc_dnum); if (c->ifc_tmp) { cudaFree(c->ifc_tmp); c->ifc_tmp = nullptr; } c->ifc_T = 0; c->ifc_ncut_alloc = 0; c->general_csr = false;
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
     dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->iAb); dfree(&c->parts); dfree(&c->scal);
     dfree(&c->ob_alpha); dfree(&c->ob_beta); dfree(&c->ob_gamma); dfree(&c->ob_xprev); dfree(&c->ob_inA); c->ob_ready = false;
@@ -260,6 +266,7 @@ extern "C" pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table) {
     return PB_OK;
 }
 #include "pb_api_cut.inl"
+static pb_status scatter_system(pb_ctx* ctx);
 #include "pb_api_interface.inl"
 
 // ------------------------------------------------------------------------------------------------ stage 1+2

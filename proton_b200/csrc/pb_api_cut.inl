@@ -5,7 +5,7 @@ extern "C" pb_status pb_cut_levelset(pb_ctx* ctx, int kind, double radius, doubl
     if (!ctx) return PB_ERR_INVALID;
     NEED(kind == 0 || kind == 1, PB_ERR_INVALID, "pb_cut_levelset: kind must be 0 (circle) or 1 (line)");
     ctx->ls.kind = kind; ctx->ls.radius = radius; ctx->ls.cx = cx; ctx->ls.cy = cy; ctx->ls.cut_y = cut_y;
-    ctx->have_ls = true; ctx->assembled = false;
+    ctx->have_ls = true; ctx->assembled = false; ctx->ifc_struct_ok = false;
     return PB_OK;
 }
 
@@ -69,7 +69,7 @@ extern "C" pb_status pb_cut_preprocess(pb_ctx* ctx, int refine_steps) {
         }
     }
     cudaFree(tmp); cudaFree(disp); cudaFree(displaced); cudaFree(is_cut); cudaFree(slot); cudaFree(err); cudaFree(p01);
-    ctx->have_cut = rc == PB_OK; ctx->assembled = false;
+    ctx->have_cut = rc == PB_OK; ctx->assembled = false; ctx->ifc_struct_ok = false;
     return rc;
 }
 
@@ -101,7 +101,7 @@ extern "C" pb_status pb_cut_upload(pb_ctx* ctx, const int* node_location, const 
         CK(cudaMemcpy(ctx->cut_cells, cells.data(), cells.size() * 4, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(ctx->iface, pts.data(), pts.size() * 8, cudaMemcpyHostToDevice));
     }
-    ctx->have_cut = true; ctx->assembled = false;
+    ctx->have_cut = true; ctx->assembled = false; ctx->ifc_struct_ok = false;
     return PB_OK;
 }
 

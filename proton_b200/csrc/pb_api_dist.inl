@@ -125,7 +125,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     if (!ctx->x) {
         CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
         CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
-        CK(dalloc(ctx, &ctx->parts, (size_t)3 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
+        CK(dalloc(ctx, &ctx->parts, (size_t)4 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
         CK(cudaMemsetAsync(ctx->dfull, 0, (size_t)nfull * 8, ctx->stream));
     }
     ctx->d = ctx->dfull + down;
@@ -133,7 +133,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
     int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
     long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
-    double *p_dy = ctx->parts, *p_rr = ctx->parts + PCG_MAX_BLOCKS, *p_rz = ctx->parts + 2 * PCG_MAX_BLOCKS;
+    double *p_dy = ctx->parts, *p_rr = ctx->parts + 2 * PCG_MAX_BLOCKS, *p_rz = ctx->parts + 3 * PCG_MAX_BLOCKS;      // d.y: block SpMV partials, then the irregular-row pass
     double *s_dy = ctx->scal, *s_rr = ctx->scal + 1, *s_rz = ctx->scal + 2;
     // what the consuming kernels read: the per-block partials (one rank) or the all-reduced scalars (several)
     const double *c_dy = multi ? s_dy : p_dy, *c_rr = multi ? s_rr : p_rr, *c_rz = multi ? s_rz : p_rz;
@@ -143,7 +143,9 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     if (blockpre && !ctx->iAb) CK(dalloc(ctx, &ctx->iAb, (size_t)n * F));
     const long long nbr_own = n / F;
     const int lpr = spmv_lanes(F);
-    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || ctx->general_csr;   // scalar CSR: comparison runs, and F = 1 where a
+    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || (ctx->general_csr && !ctx->ifc_struct_ok);
+    // interface problem: block kernel on the block rows in interface order + a scalar pass over the rows of the cut cells' faces
+    const int nblk_irr = (!use_csr && ctx->general_csr && ctx->n_irr_rows > 0) ? (int)std::min<long long>(nsm, ((long long)ctx->n_irr_rows * F + 7) / 8) : 0;   // one warp per scalar row   // scalar CSR: comparison runs, and F = 1 where a
                                                                                // 64-byte face record per row costs more than 7 column indices
     int nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
     if (!use_csr) {
@@ -151,7 +153,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
         nblk_sp = nsm * occ; if (nblk_sp > PCG_MAX_BLOCKS) nblk_sp = PCG_MAX_BLOCKS;
         const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < nblk_sp) nblk_sp = (int)(wantg < 1 ? 1 : wantg);
     }
-    const int c_ndy = multi ? 1 : nblk_sp;
+    const int c_ndy = multi ? 1 : nblk_sp + nblk_irr;
     cudaStream_t sm = ctx->stream;
     auto reduce_rr_rz = [&]() -> pb_status {
         if (!multi) return PB_OK;
@@ -187,6 +189,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
             switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
         }
 #undef PB_SPMV
+        if (nblk_irr) pcg_spmv_rows_kernel<<<nblk_irr, PCG_THREADS, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, ctx->y, p_dy + nblk_sp, ctx->cg);
         if (multi) {
             pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk_sp, p_dy, s_dy, nullptr, nullptr);
             NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));

@@ -94,7 +94,7 @@ static cudaError_t launch_ifc_t(pb_ctx* c, const IfcArgs& A) {
     auto kern = local_cut_interface_kernel<CD, FD>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    int grid = A.ncut < 148 * 4 ? A.ncut : 148 * 4;
+    int grid = A.ncut < 148 * 8 ? A.ncut : 148 * 8;
     kern<<<grid, 32, smem, c->stream>>>(A);
     return cudaGetLastError();
 }
@@ -103,9 +103,13 @@ static cudaError_t launch_ifc_t(pb_ctx* c, const IfcArgs& A) {
 static pb_status launch_interface_cut(pb_ctx* ctx, const pb_assembly_params* p, int cd, int fd) {
     const int C = ctx->C, NF = ctx->NF, N2 = 2 * C + 2 * NF;
     const size_t nc = (size_t)(ctx->ncut > 0 ? ctx->ncut : 1);
-    CK(dalloc(ctx, &ctx->Sx, nc * 4 * NF * NF)); CK(dalloc(ctx, &ctx->gx, nc * 2 * NF));
-    CK(dalloc(ctx, &ctx->recAx, nc * 4 * NF * C)); CK(dalloc(ctx, &ctx->recbx, nc * 2 * C));
-    if (p->keep_local) { CK(dalloc(ctx, &ctx->lcx, nc * N2 * N2)); CK(dalloc(ctx, &ctx->fx, nc * 2 * C)); }
+    if (!ctx->Sx || ctx->ifc_ncut_alloc != (long long)nc) {          // kept across assemblies of the same cut mesh
+        CK(dalloc(ctx, &ctx->Sx, nc * 4 * NF * NF)); CK(dalloc(ctx, &ctx->gx, nc * 2 * NF));
+        CK(dalloc(ctx, &ctx->recAx, nc * 4 * NF * C)); CK(dalloc(ctx, &ctx->recbx, nc * 2 * C));
+        dfree(&ctx->lcx); dfree(&ctx->fx);
+        ctx->ifc_ncut_alloc = (long long)nc;
+    }
+    if (p->keep_local) { if (!ctx->lcx) { CK(dalloc(ctx, &ctx->lcx, nc * N2 * N2)); CK(dalloc(ctx, &ctx->fx, nc * 2 * C)); } }
     else { dfree(&ctx->lcx); dfree(&ctx->fx); }
     if (ctx->ncut == 0) return PB_OK;
     IfcArgs A{};
@@ -123,7 +127,7 @@ static pb_status launch_interface_cut(pb_ctx* ctx, const pb_assembly_params* p, 
 }
 
 // condensed system in interface_assembler's numbering: triplets -> radix sort -> sum of duplicates -> CSR
-static pb_status build_interface_system(pb_ctx* ctx) {
+static pb_status build_interface_system_sorted(pb_ctx* ctx) {
     const Grid& g = ctx->grid; const int F = ctx->F, NF = ctx->NF;
     const long long nc = g.Nx * g.Ny, nf = ctx->nfaces;
     cudaStream_t sm = ctx->stream;
@@ -187,6 +191,286 @@ static pb_status build_interface_system(pb_ctx* ctx) {
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(sm);
     release();
+    if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_assemble: interface system kernels failed: %s", cudaGetErrorString(e));
+    return PB_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// Hybrid system build (default).  Rows of a face whose two cells are uncut keep the closed-form block row of the plain
+// problems — only their column blocks move, by the number of cut faces before them — so K3 (and the block SpMV) serve
+// them unchanged from a BlockRow table in interface order.  Only the rows of the cut cells' faces ("irregular": their
+// four faces, both sets of the cut ones; about 4 ncut block rows) are built from sorted triplets.  All rows still come in
+// groups of fbs with fbs-wide column blocks, so one brp / rowptr layout covers both kinds.
+
+__global__ void ifc_flag_irregular_kernel(Grid g, int ncut, const int* __restrict__ cut_cells, int* __restrict__ irr) {
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < ncut; s += gridDim.x * blockDim.x) {
+        const long long c = cut_cells[s], ci = c % g.Nx, cj = c / g.Nx;
+        long long f[4]; cell_faces(g, ci, cj, f);
+        for (int li = 0; li < 4; li++) if (!cell_face_dirichlet(g, ci, cj, li)) irr[f[li]] = 1;
+    }
+}
+// face id -> the two cells of a free face and the local index of the face in each (as build_block_rows_kernel)
+__device__ __forceinline__ bool ifc_face_cells(const Grid& g, long long f, long long ci[2], long long cj[2], int li[2]) {
+    const long long per = 2 * g.Nx + 1, j = f / per, rem = f - j * per;
+    if (j >= g.Ny) return false;                              // top boundary
+    if (rem == 2 * g.Nx) return false;                        // right boundary
+    if ((rem & 1) == 0) { const long long i = rem / 2; if (j == 0) return false; ci[0] = i; cj[0] = j - 1; li[0] = 2; ci[1] = i; cj[1] = j; li[1] = 0; return true; }
+    const long long i = (rem - 1) / 2; if (i == 0) return false;
+    ci[0] = i - 1; cj[0] = j; li[0] = 1; ci[1] = i; cj[1] = j; li[1] = 3; return true;
+}
+constexpr unsigned long long IFC_NOKEY = ~0ull;
+// triplets of the irregular rows: per (irregular face, adjacent cell) a fixed window of 4*F*NF entries
+__global__ void ifc_irregular_triplets_kernel(Grid g, int F, int nirr, const int* __restrict__ irr_faces, const int* __restrict__ cell_loc, int ncut,
+                                              const int* __restrict__ cut_cells, const int* __restrict__ face_loc, const int* __restrict__ ftab, long long n,
+                                              const double* __restrict__ S, const double* __restrict__ Sx, unsigned long long* __restrict__ keys, double* __restrict__ vals) {
+    const int NF = 4 * F, NF2 = 2 * NF, win = 4 * F * NF;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)nirr * 2 * win; t += (long long)gridDim.x * blockDim.x) {
+        const long long q = t / (2 * win); const int r = (int)(t - q * 2 * win), k = r / win, e = r - k * win;
+        unsigned long long key = IFC_NOKEY; double v = 0.0;
+        long long ci[2], cj[2]; int li[2];
+        if (ifc_face_cells(g, irr_faces[q], ci, cj, li)) {
+            const long long c = cj[k] * g.Nx + ci[k];
+            long long f[4]; cell_faces(g, ci[k], cj[k], f);
+            if (cell_loc[c] != PB_ON_INTERFACE) {
+                if (e < F * NF) {             // rows (li, a), all columns
+                    const int a = e / NF, jj = e - a * NF, lj = jj / F;
+                    if (!cell_face_dirichlet(g, ci[k], cj[k], lj)) {
+                        const long long row = (long long)ftab[f[li[k]]] * F + a, col = (long long)ftab[f[lj]] * F + (jj - lj * F);
+                        key = (unsigned long long)row * (unsigned long long)n + (unsigned long long)col;
+                        v = S[c * (long long)(NF * NF) + (li[k] * F + a) + (long long)jj * NF];
+                    }
+                }
+            } else {
+                int lo = 0, hi = ncut - 1;
+                while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
+                const int sd = e / (F * NF2), r2 = e - sd * (F * NF2), a = r2 / NF2, tc = r2 - a * NF2, tr = sd * NF + li[k] * F + a;
+                const long long row = ifc_slot_dof(g, F, face_loc, ftab, f, tr), col = ifc_slot_dof(g, F, face_loc, ftab, f, tc);
+                key = (unsigned long long)row * (unsigned long long)n + (unsigned long long)col;
+                v = Sx[lo * (long long)(NF2 * NF2) + tr + (long long)tc * NF2];
+            }
+        }
+        keys[t] = key; vals[t] = v;
+    }
+}
+__device__ __forceinline__ long long ifc_lower_bound(const unsigned long long* k, long long n, unsigned long long want) {
+    long long lo = 0, hi = n;
+    while (lo < hi) { const long long mid = (lo + hi) / 2; if (k[mid] < want) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+// one thread per face: block row(s) of the face in interface order.  Regular face: the closed-form block row with the
+// column blocks renumbered by face_table; irregular face: an empty BlockRow (K3 and the block SpMV skip it) and the
+// number of column blocks counted in the sorted irregular entries.
+__global__ void ifc_block_rows_kernel(Grid g, int F, long long nfaces, const int* __restrict__ ftab, const int* __restrict__ irr, const int* __restrict__ face_loc,
+                                      long long n, const unsigned long long* __restrict__ ukeys, long long nuniq, BlockRow* __restrict__ rows, int* __restrict__ nb_all) {
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nfaces; f += (long long)gridDim.x * blockDim.x) {
+        if (ftab[f + 1] == ftab[f]) continue;                // Dirichlet
+        const long long s = ftab[f];
+        long long ci[2], cj[2]; int li[2];
+        ifc_face_cells(g, f, ci, cj, li);
+        BlockRow br; memset(&br, 0, sizeof br);
+        if (irr[f]) {
+            const int sets = face_loc[f] == PB_ON_INTERFACE ? 2 : 1;
+            for (int k = 0; k < sets; k++) {
+                const unsigned long long r0 = (unsigned long long)((s + k) * F) * (unsigned long long)n;
+                const long long len = ifc_lower_bound(ukeys, nuniq, r0 + (unsigned long long)n) - ifc_lower_bound(ukeys, nuniq, r0);
+                for (int m = 0; m < 7; m++) { br.bcol[m] = -1; br.src[0][m] = 255; br.src[1][m] = 255; }
+                rows[s + k] = br; nb_all[s + k] = (int)(len / F);
+            }
+            continue;
+        }
+        long long ids[8]; unsigned char s0[8], s1[8]; int cnt = 0;
+        for (int k = 0; k < 2; k++) {
+            br.cell[k] = (int)(cj[k] * g.Nx + ci[k]); br.li[k] = (unsigned char)li[k];
+            long long fc[4]; cell_faces(g, ci[k], cj[k], fc);
+            for (int lf = 0; lf < 4; lf++) {
+                if (cell_face_dirichlet(g, ci[k], cj[k], lf)) continue;
+                const long long id = ftab[fc[lf]];
+                int pos = -1;
+                for (int m = 0; m < cnt; m++) if (ids[m] == id) pos = m;
+                if (pos < 0) { pos = cnt++; ids[pos] = id; s0[pos] = 255; s1[pos] = 255; }
+                if (k == 0) s0[pos] = (unsigned char)lf; else s1[pos] = (unsigned char)lf;
+            }
+        }
+        for (int a = 1; a < cnt; a++) {
+            long long id = ids[a]; unsigned char x0 = s0[a], x1 = s1[a]; int b = a - 1;
+            while (b >= 0 && ids[b] > id) { ids[b + 1] = ids[b]; s0[b + 1] = s0[b]; s1[b + 1] = s1[b]; b--; }
+            ids[b + 1] = id; s0[b + 1] = x0; s1[b + 1] = x1;
+        }
+        br.nb = (unsigned char)cnt;
+        for (int m = 0; m < 7; m++) { br.bcol[m] = m < cnt ? (int)ids[m] : -1; br.src[0][m] = m < cnt ? s0[m] : 255; br.src[1][m] = m < cnt ? s1[m] : 255; }
+        rows[s] = br; nb_all[s] = cnt;
+    }
+}
+// rowptr of every scalar row; columns of the regular rows
+__global__ void ifc_pattern_kernel(long long nslots, int F, const BlockRow* __restrict__ rows, const int* __restrict__ nb_all, const long long* __restrict__ brp,
+                                   long long* __restrict__ rowptr, int* __restrict__ col) {
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t <= nslots * F; t += (long long)gridDim.x * blockDim.x) {
+        if (t == nslots * F) { rowptr[t] = brp[nslots] * F * F; continue; }
+        const long long s = t / F; const int a = (int)(t - s * F);
+        const long long base = brp[s] * F * F + (long long)a * nb_all[s] * F;
+        rowptr[t] = base;
+        const BlockRow& R = rows[s];
+        for (int b = 0; b < R.nb; b++) for (int bc = 0; bc < F; bc++) col[base + b * F + bc] = R.bcol[b] * F + bc;
+    }
+}
+// columns and values of the irregular rows from the sorted, summed entries
+__global__ void ifc_irregular_fill_kernel(long long nuniq, long long n, const unsigned long long* __restrict__ ukeys, const double* __restrict__ uvals,
+                                          const long long* __restrict__ rowptr, int* __restrict__ col, double* __restrict__ val) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < nuniq; e += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long key = ukeys[e];
+        if (key == IFC_NOKEY) continue;
+        const unsigned long long r = key / (unsigned long long)n;
+        const long long lo = ifc_lower_bound(ukeys, nuniq, r * (unsigned long long)n);
+        const long long dst = rowptr[r] + (e - lo);
+        col[dst] = (int)(key - r * (unsigned long long)n); val[dst] = uvals[e];
+    }
+}
+// rows of the irregular block rows, for the scalar SpMV pass
+__global__ void ifc_irregular_rows_kernel(long long nslots, int F, const BlockRow* __restrict__ rows, const int* __restrict__ nb_all, int* __restrict__ flags) {
+    for (long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x; s < nslots; s += (long long)gridDim.x * blockDim.x)
+        flags[s] = (rows[s].nb == 0 && nb_all[s] > 0) ? 1 : 0;
+}
+
+// rhs of the irregular rows: zeroed, then the <= 2 cells of every irregular face add their part (K3 has written the others)
+__global__ void ifc_zero_rhs_rows_kernel(int nrows_irr, int F, const int* __restrict__ irr_rows, double* __restrict__ rhs) {
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nrows_irr * F; t += gridDim.x * blockDim.x) rhs[(long long)irr_rows[t / F] * F + (t % F)] = 0.0;
+}
+__global__ void ifc_irregular_rhs_kernel(Grid g, int F, int nirr, const int* __restrict__ irr_faces, const int* __restrict__ cell_loc, int ncut,
+                                         const int* __restrict__ cut_cells, const int* __restrict__ face_loc, const int* __restrict__ ftab,
+                                         const double* __restrict__ gv, const double* __restrict__ gx, double* __restrict__ rhs) {
+    const int NF = 4 * F, win = 2 * F;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)nirr * 2 * win; t += (long long)gridDim.x * blockDim.x) {
+        const long long q = t / (2 * win); const int r = (int)(t - q * 2 * win), k = r / win, e = r - k * win;
+        long long ci[2], cj[2]; int li[2];
+        if (!ifc_face_cells(g, irr_faces[q], ci, cj, li)) continue;
+        const long long c = cj[k] * g.Nx + ci[k];
+        long long f[4]; cell_faces(g, ci[k], cj[k], f);
+        if (cell_loc[c] != PB_ON_INTERFACE) {
+            if (e < F) atomicAdd(rhs + (long long)ftab[f[li[k]]] * F + e, gv[c * NF + li[k] * F + e]);
+        } else {
+            int lo = 0, hi = ncut - 1;
+            while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
+            const int sd = e / F, a = e - sd * F, tr = sd * NF + li[k] * F + a;
+            const double v = gx[(long long)lo * 2 * NF + tr];
+            if (v != 0.0) atomicAdd(rhs + ifc_slot_dof(g, F, face_loc, ftab, f, tr), v);
+        }
+    }
+}
+
+// sorted, summed entries of the irregular rows (values of the current S / Sx) in buffers kept with the structure
+struct IfcSorted { unsigned long long* uk = nullptr; double* uv = nullptr; long long nuniq = 0; void release() {} };
+static pb_status ifc_sorted_irregular(pb_ctx* ctx, IfcSorted& R) {
+    const Grid& g = ctx->grid; const int F = ctx->F, NF = ctx->NF; cudaStream_t sm = ctx->stream;
+    const int nirr = ctx->n_irr_faces; const long long n = ctx->nrows;
+    const long long T = (long long)(nirr > 0 ? nirr : 1) * 2 * 4 * F * NF;
+    if (ctx->ifc_T != T || !ctx->ifc_k0) {
+        dfree(&ctx->ifc_k0); dfree(&ctx->ifc_k1); dfree(&ctx->ifc_v0); dfree(&ctx->ifc_v1); dfree(&ctx->ifc_dnum);
+        if (ctx->ifc_tmp) { cudaFree(ctx->ifc_tmp); ctx->ifc_tmp = nullptr; }
+        CK(dalloc(ctx, &ctx->ifc_k0, (size_t)T)); CK(dalloc(ctx, &ctx->ifc_k1, (size_t)T)); CK(dalloc(ctx, &ctx->ifc_v0, (size_t)T)); CK(dalloc(ctx, &ctx->ifc_v1, (size_t)T));
+        CK(dalloc(ctx, &ctx->ifc_dnum, 1));
+        cub::DoubleBuffer<unsigned long long> dk(ctx->ifc_k0, ctx->ifc_k1); cub::DoubleBuffer<double> dv(ctx->ifc_v0, ctx->ifc_v1);
+        size_t t1 = 0, t2 = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, T, 0, 64, sm));
+        CK(cub::DeviceReduce::ReduceByKey(nullptr, t2, ctx->ifc_k0, ctx->ifc_k1, ctx->ifc_v0, ctx->ifc_v1, ctx->ifc_dnum, cuda::std::plus<>(), T, sm));
+        ctx->ifc_tmp_bytes = t1 > t2 ? t1 : t2;
+        CK(cudaMalloc(&ctx->ifc_tmp, ctx->ifc_tmp_bytes));
+        ctx->ifc_T = T;
+    }
+    CK(cudaMemsetAsync(ctx->ifc_k0, 0xff, (size_t)T * 8, sm)); CK(cudaMemsetAsync(ctx->ifc_v0, 0, (size_t)T * 8, sm));
+    if (nirr > 0)
+        ifc_irregular_triplets_kernel<<<148 * 4, 256, 0, sm>>>(g, F, nirr, ctx->irr_faces, ctx->cell_loc_g, ctx->ncut, ctx->cut_cells, ctx->face_loc, ctx->ftab, n, ctx->S, ctx->Sx,
+                                                              ctx->ifc_k0, ctx->ifc_v0);
+    cub::DoubleBuffer<unsigned long long> dk(ctx->ifc_k0, ctx->ifc_k1); cub::DoubleBuffer<double> dv(ctx->ifc_v0, ctx->ifc_v1);
+    size_t tb = ctx->ifc_tmp_bytes;
+    CK(cub::DeviceRadixSort::SortPairs(ctx->ifc_tmp, tb, dk, dv, T, 0, 64, sm));          // stable: equal keys keep the generation order
+    R.uk = dk.Alternate(); R.uv = dv.Alternate();
+    tb = ctx->ifc_tmp_bytes;
+    CK(cub::DeviceReduce::ReduceByKey(ctx->ifc_tmp, tb, dk.Current(), R.uk, dv.Current(), R.uv, ctx->ifc_dnum, cuda::std::plus<>(), T, sm));
+    CK(cudaMemcpyAsync(&R.nuniq, ctx->ifc_dnum, 8, cudaMemcpyDeviceToHost, sm));
+    CK(cudaStreamSynchronize(sm));
+    return PB_OK;
+}
+
+static pb_status build_interface_system(pb_ctx* ctx) {
+    if (getenv("PB_IFC_SORT_ALL")) return build_interface_system_sorted(ctx);        // the first version, kept for comparison
+    const Grid& g = ctx->grid; const int F = ctx->F;
+    const long long nf = ctx->nfaces;
+    cudaStream_t sm = ctx->stream;
+    IfcSorted R;
+    if (!ctx->ifc_struct_ok) {
+        // ---- structure, once per mesh / level set / degree: face_table, irregular faces, block rows, brp, CSR pattern
+        int *w = nullptr, *irr = nullptr, *dcount = nullptr, *nb_all = nullptr, *fl = nullptr; void* tmp = nullptr;
+        auto release = [&]() { cudaFree(w); cudaFree(irr); cudaFree(dcount); cudaFree(nb_all); cudaFree(fl); cudaFree(tmp); R.release(); };
+#define IFC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { release(); return fail(ctx, PB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } } while (0)
+        IFC(cudaMalloc((void**)&w, (size_t)(nf + 1) * 4)); IFC(cudaMalloc((void**)&irr, (size_t)(nf + 1) * 4)); IFC(cudaMalloc((void**)&dcount, 4));
+        IFC(dalloc(ctx, &ctx->irr_faces, (size_t)nf + 1));
+        IFC(cudaMemsetAsync(w, 0, (size_t)(nf + 1) * 4, sm)); IFC(cudaMemsetAsync(irr, 0, (size_t)(nf + 1) * 4, sm));
+        ifc_face_weight_kernel<<<148 * 8, 256, 0, sm>>>(g, ctx->face_loc, w);
+        if (ctx->ncut > 0) ifc_flag_irregular_kernel<<<(ctx->ncut + 255) / 256, 256, 0, sm>>>(g, ctx->ncut, ctx->cut_cells, irr);
+        IFC(dalloc(ctx, &ctx->ftab, (size_t)nf + 1));
+        size_t tb = 0;
+        IFC(cub::DeviceScan::ExclusiveSum(nullptr, tb, w, ctx->ftab, (int)(nf + 1), sm));
+        IFC(cudaMalloc(&tmp, tb));
+        IFC(cub::DeviceScan::ExclusiveSum(tmp, tb, w, ctx->ftab, (int)(nf + 1), sm));
+        cudaFree(tmp); tmp = nullptr; tb = 0;
+        IFC(cub::DeviceSelect::Flagged(nullptr, tb, cub::CountingInputIterator<int>(0), irr, ctx->irr_faces, dcount, (int)nf, sm));
+        IFC(cudaMalloc(&tmp, tb));
+        IFC(cub::DeviceSelect::Flagged(tmp, tb, cub::CountingInputIterator<int>(0), irr, ctx->irr_faces, dcount, (int)nf, sm));
+        int nslots = 0, nirr = 0;
+        IFC(cudaMemcpyAsync(&nslots, ctx->ftab + nf, 4, cudaMemcpyDeviceToHost, sm));
+        IFC(cudaMemcpyAsync(&nirr, dcount, 4, cudaMemcpyDeviceToHost, sm));
+        IFC(cudaStreamSynchronize(sm));
+        cudaFree(tmp); tmp = nullptr;
+        const long long n = (long long)nslots * F;
+        if (n >= (1ll << 31)) { release(); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: interface system too large for 32-bit column indices"); }
+        ctx->nrows = n; ctx->nrows_blk = nslots; ctx->n_irr_faces = nirr;
+        { pb_status st = ifc_sorted_irregular(ctx, R); if (st != PB_OK) { release(); return st; } }
+        IFC(dalloc(ctx, &ctx->brows, (size_t)nslots)); IFC(dalloc(ctx, &ctx->brp, (size_t)nslots + 1));
+        IFC(cudaMalloc((void**)&nb_all, (size_t)(nslots + 1) * 4));
+        IFC(cudaMemsetAsync(nb_all, 0, (size_t)(nslots + 1) * 4, sm));
+        ifc_block_rows_kernel<<<148 * 8, 256, 0, sm>>>(g, F, nf, ctx->ftab, irr, ctx->face_loc, n, R.uk, R.nuniq, ctx->brows, nb_all);
+        tb = 0;
+        IFC(cub::DeviceScan::ExclusiveScan(nullptr, tb, nb_all, ctx->brp, cuda::std::plus<>(), 0LL, nslots + 1, sm));
+        IFC(cudaMalloc(&tmp, tb));
+        IFC(cub::DeviceScan::ExclusiveScan(tmp, tb, nb_all, ctx->brp, cuda::std::plus<>(), 0LL, nslots + 1, sm));
+        long long nblk = 0;
+        IFC(cudaMemcpyAsync(&nblk, ctx->brp + nslots, 8, cudaMemcpyDeviceToHost, sm));
+        IFC(cudaStreamSynchronize(sm));
+        cudaFree(tmp); tmp = nullptr;
+        ctx->nnz = nblk * F * F;
+        IFC(dalloc(ctx, &ctx->rowptr, (size_t)n + 1)); IFC(dalloc(ctx, &ctx->col, (size_t)ctx->nnz));
+        IFC(dalloc(ctx, &ctx->val, (size_t)ctx->nnz)); IFC(dalloc(ctx, &ctx->rhs, (size_t)n));
+        ifc_pattern_kernel<<<148 * 8, 256, 0, sm>>>(nslots, F, ctx->brows, nb_all, ctx->brp, ctx->rowptr, ctx->col);
+        // list of the irregular block rows (rhs fix-up, scalar SpMV pass of pb_pcg)
+        IFC(cudaMalloc((void**)&fl, (size_t)(nslots + 1) * 4));
+        ifc_irregular_rows_kernel<<<148 * 4, 256, 0, sm>>>(nslots, F, ctx->brows, nb_all, fl);
+        IFC(dalloc(ctx, &ctx->irr_rows, (size_t)(2 * (nirr > 0 ? nirr : 1))));
+        tb = 0;
+        IFC(cub::DeviceSelect::Flagged(nullptr, tb, cub::CountingInputIterator<int>(0), fl, ctx->irr_rows, dcount, nslots, sm));
+        IFC(cudaMalloc(&tmp, tb));
+        IFC(cub::DeviceSelect::Flagged(tmp, tb, cub::CountingInputIterator<int>(0), fl, ctx->irr_rows, dcount, nslots, sm));
+        int nir = 0;
+        IFC(cudaMemcpyAsync(&nir, dcount, 4, cudaMemcpyDeviceToHost, sm));
+        IFC(cudaStreamSynchronize(sm));
+        ctx->n_irr_rows = nir;
+        cudaFree(w); cudaFree(irr); cudaFree(dcount); cudaFree(nb_all); cudaFree(fl); cudaFree(tmp);
+#undef IFC
+        ctx->ifc_struct_ok = true;
+    } else {
+        pb_status st = ifc_sorted_irregular(ctx, R); if (st != PB_OK) return st;
+    }
+    // ---- values: irregular rows from the sorted entries (their columns too), regular rows and their rhs by K3, rhs of the irregular rows
+    const long long n = ctx->nrows;
+    ifc_irregular_fill_kernel<<<148 * 4, 256, 0, sm>>>(R.nuniq, n, R.uk, R.uv, ctx->rowptr, ctx->col, ctx->val);
+    { pb_status st = scatter_system(ctx); if (st != PB_OK) { R.release(); return st; } }
+    if (ctx->n_irr_rows > 0) {
+        ifc_zero_rhs_rows_kernel<<<(ctx->n_irr_rows * F + 255) / 256, 256, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rhs);
+        ifc_irregular_rhs_kernel<<<148 * 2, 256, 0, sm>>>(g, F, ctx->n_irr_faces, ctx->irr_faces, ctx->cell_loc_g, ctx->ncut, ctx->cut_cells, ctx->face_loc, ctx->ftab, ctx->g, ctx->gx, ctx->rhs);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(sm);
+    R.release();
     if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_assemble: interface system kernels failed: %s", cudaGetErrorString(e));
     return PB_OK;
 }

@@ -157,10 +157,30 @@ __global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow*
         for (int a = 0; a < F; a++)
 #pragma unroll
             for (int o = LPR / 2; o > 0; o >>= 1) acc[a] += __shfl_down_sync(0xffffffffu, acc[a], o, LPR);
-        if (sub == 0 && br < nbr) {
+        if (sub == 0 && br < nbr && rows[br].nb) {          // empty block rows (interface problem) belong to pcg_spmv_rows_kernel
 #pragma unroll
             for (int a = 0; a < F; a++) { y[br * F + a] = acc[a]; dy += acc[a] * dvec[down + br * F + a]; }
         }
+    }
+    double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
+}
+
+// scalar rows of a short list of block rows (interface problem: the rows of the cut cells' faces, which the block kernel
+// leaves at zero); one thread per scalar row, partial sums of d.y appended after the block kernel's
+__global__ void pcg_spmv_rows_kernel(int nbrows, int F, const int* __restrict__ brow_list, const long long* __restrict__ rowptr, const int* __restrict__ col,
+                                     const double* __restrict__ val, const double* __restrict__ dvec, double* __restrict__ y, double* __restrict__ parts_dy,
+                                     const CgState* st) {
+    __shared__ double sh[32];
+    if (st->done) return;
+    const int lane = threadIdx.x & 31, nwarps = (gridDim.x * blockDim.x) >> 5;
+    double dy = 0.0;
+    for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < nbrows * F; t += nwarps) {        // one warp per scalar row
+        const long long r = (long long)brow_list[t / F] * F + (t % F);
+        double acc = 0.0;
+        for (long long k = rowptr[r] + lane; k < rowptr[r + 1]; k += 32) acc += val[k] * dvec[col[k]];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) { y[r] = acc; dy += acc * dvec[r]; }
     }
     double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
 }
