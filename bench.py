@@ -172,6 +172,32 @@ def cut_record(args, rank, world, dev, dist, torch, pb, PB):
             "pcg_ms_per_iter": vals[1], "pcg_hbm_frac": iter_bytes / (vals[1] * 1e-3) / 1e9 / hbm, "unknowns": rows, "nnz": nnz}
 
 
+def interface_record(args, dev, pb, PB):
+    """Secondary record (single GPU): the two-material interface problem of `cuthho_square -i`, k=2, circle level
+    set r=0.35, on ifc_N x ifc_N quads: preprocessing, repeated assembly (K1 + K2i + K3 + sorted rows of the cut cells' faces), a
+    fixed number of PCG iterations."""
+    Nc, k = args.ifc_N, 2
+    hdi = pb.hho_degree_info(k + 1, k)
+    ctx = pb.Context(dev)
+    ctx.mesh(pb.mesh_init_params(Nc, Nc), PB.QUAD_POLY_DUNAVANT)
+    ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
+    ms = []
+    for i in range(5):
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        t = ctx.timings()
+        if i >= 2:
+            ms.append((t["ms_local"], t["ms_scatter"]))
+    loc = sum(m[0] for m in ms) / len(ms); sysb = sum(m[1] for m in ms) / len(ms)
+    ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 20, True))
+    ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 100, True))
+    it_ms = ctx.timings()["ms_pcg"] / 101.0
+    out = {"workload": f"cutHHO two-material interface problem (cuthho_square -i) k=2, circle level set r=0.35, {Nc}x{Nc} quads, one GPU",
+           "cut_cells": ctx.cut_counts()[0], "unknowns": ctx.n_rows, "nnz": ctx.nnz, "local_ms": loc, "system_ms": sysb,
+           "cells_per_s": Nc * Nc / ((loc + sysb) * 1e-3), "pcg_ms_per_iter": it_ms}
+    ctx.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -322,6 +348,8 @@ def run_ours(args, rank, world, local_rank):
     ctx.close()
     if not args.no_cut:
         out["target_cut"] = cut_record(args, rank, world, dev, dist, torch, pb, PB)
+    if world == 1 and not args.no_interface:
+        out["interface"] = interface_record(args, dev, pb, PB)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
@@ -352,6 +380,8 @@ def main():
     ap.add_argument("--no-cg-tol", action="store_true", help="skip the solve-to-tolerance run (fixed-iteration bandwidth run only)")
     ap.add_argument("--no-cut", action="store_true", help="skip the secondary cutHHO record")
     ap.add_argument("--cut-N", dest="cut_N", type=int, default=4096)
+    ap.add_argument("--no-interface", action="store_true", help="skip the secondary record of the two-material interface problem")
+    ap.add_argument("--ifc-N", dest="ifc_N", type=int, default=2048)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -145,7 +145,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     const int lpr = spmv_lanes(F);
     const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || (ctx->general_csr && !ctx->ifc_struct_ok);
     // interface problem: block kernel on the block rows in interface order + a scalar pass over the rows of the cut cells' faces
-    const int nblk_irr = (!use_csr && ctx->general_csr && ctx->n_irr_rows > 0) ? (int)std::min<long long>(nsm, ((long long)ctx->n_irr_rows * F + 7) / 8) : 0;   // one warp per scalar row   // scalar CSR: comparison runs, and F = 1 where a
+    const int nblk_irr = (!use_csr && ctx->general_csr && ctx->n_irr_rows > 0) ? (int)std::min<long long>(PCG_MAX_BLOCKS, ((long long)ctx->n_irr_rows * F + 7) / 8) : 0;   // one warp per scalar row   // scalar CSR: comparison runs, and F = 1 where a
                                                                                // 64-byte face record per row costs more than 7 column indices
     int nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
     if (!use_csr) {

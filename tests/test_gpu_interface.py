@@ -104,3 +104,67 @@ def test_interface_golden_through_the_gpu_path(ctx, golden, k, N):
     ref = golden["cuthho_interface"][f"k{k}_N{N}_r4"]
     assert abs(np.sqrt(ctx.error_norms()[0]) - ref) / ref < 1e-5
     assert abs(S.h1_error(ctx.recover()) - ref) / ref < 1e-5
+
+
+@pytest.mark.parametrize("k,N", [(1, 64), (2, 96)])
+def test_interface_hybrid_system_equals_all_sorted_system(k, N):
+    """the default build (K3 + block rows in interface order for the rows of uncut faces, sorted triplets for the cut
+    cells' faces) gives the pattern of the all-sorted first version (PB_IFC_SORT_ALL=1) bit for bit and its values to
+    rounding (K3 reads the transposed entry of the symmetric cell block); both symmetric; same PCG iteration count +-1."""
+    import os
+    got = {}
+    for mode in ("hybrid", "sorted"):
+        if mode == "sorted":
+            os.environ["PB_IFC_SORT_ALL"] = "1"
+        try:
+            c = pb.Context(0)
+            c.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT)
+            c.cut_levelset(0, 0.35, 0.5, 0.5); c.cut_preprocess(4)
+            for _ in range(2):          # the second assembly takes the cached-structure path
+                c.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+            rp, col, val, rhs = c.csr()
+            res = c.conjugated_gradient(pb.cg_params(1e-12, 1e8, 50 * c.n_rows, True))
+            got[mode] = (rp, col, val, rhs, res["iterations"], c.face_solution())
+            c.close()
+        finally:
+            os.environ.pop("PB_IFC_SORT_ALL", None)
+    (rp, col, val, rhs, it, x), (rp2, col2, val2, rhs2, it2, x2) = got["hybrid"], got["sorted"]
+    assert np.array_equal(rp, rp2) and np.array_equal(col, col2)
+    scale = np.max(np.abs(val2))
+    assert np.max(np.abs(val - val2)) < 1e-13 * scale and np.max(np.abs(rhs - rhs2)) <= 1e-15 * np.max(np.abs(rhs2))
+    A = sp.csr_matrix((val, col, rp), shape=(len(rhs), len(rhs)))
+    assert abs(A - A.T).max() < 1e-11 * scale
+    assert abs(it - it2) <= 1 and frob_rel(x, x2) < 1e-8
+
+
+def test_interface_full_size_properties():
+    """1024 x 1024, k=2 (6.3 M unknowns): sizes from the cut data, sorted CSR, constants in the kernel of every row away
+    from the Dirichlet boundary (gradient, consistency, penalty and stabilisation terms all vanish on the common constant),
+    the solver runs on it."""
+    import ctypes as C
+    N, k = 1024, 2; F = k + 1
+    c = pb.Context(0)
+    try:
+        c.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT)
+        c.cut_levelset(0, 0.35, 0.5, 0.5); c.cut_preprocess(4)
+        c.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        face_loc = np.zeros(c.nfaces, np.int32)
+        assert pb.lib().pb_cut_download(c._h, None, face_loc.ctypes.data_as(C.c_void_p), None, None, None, None, None) == 0
+        ft = c.interface_face_table()
+        ncut_faces = int(((face_loc == PB.ON_INTERFACE) & (ft >= 0)).sum())
+        assert c.n_rows == (2 * N * (N - 1) + ncut_faces) * F
+        ncut = c.cut_counts()[0]
+        assert abs(ncut - 8 * 0.35 * N) < 0.01 * 8 * 0.35 * N and ncut_faces == ncut          # a closed curve cuts as many faces as cells
+        rp, col, val, rhs = c.csr()
+        assert rp[-1] == c.nnz and np.all(np.diff(rp) > 0)
+        A = sp.csr_matrix((val, col, rp), shape=(c.n_rows, c.n_rows))
+        e0 = np.zeros(c.n_rows); e0[::F] = 1.0
+        y = A @ e0
+        # rows with a full stencil (no Dirichlet face among the faces of their two cells; the cut cells' rows have more blocks)
+        interior = np.diff(rp) >= 7 * F
+        assert interior.sum() > 0.99 * c.n_rows
+        assert np.max(np.abs(y[interior])) < 1e-9 * np.max(np.abs(val)), np.max(np.abs(y[interior]))
+        res = c.conjugated_gradient(pb.cg_params(0.0, 1e300, 50, True))
+        assert res["iterations"] >= 50 and np.all(np.isfinite(c.face_solution()))
+    finally:
+        c.close()

@@ -3,7 +3,7 @@
 # 1. the plain bench must exit 0; 2. ncu launch list of the same command; 3. one --set full capture per hot kernel.
 # Outputs go to gpurun_out/TAG_*; summarise them afterwards HERE with tools/profile_summaries.py TAG.
 TAG=$1
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-cg-tol"
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-cg-tol --no-interface"
 mkdir -p gpurun_out
 $CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "plain bench failed"; tail -5 gpurun_out/${TAG}_plain.err; exit 1; }
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
