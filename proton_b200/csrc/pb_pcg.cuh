@@ -265,32 +265,40 @@ __global__ void pcg_init_blk_kernel(long long nbr, const double* __restrict__ b,
     double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
     t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;
 }
+// x += alpha d, r -= alpha y, z = iAb r: a block walks chunks of blockDim * F consecutive unknowns (whole faces) with
+// unit-stride loads, stages the new residual in shared memory and applies the F x F blocks from there
 template <int F>
-__global__ void pcg_xrz_blk_kernel(long long nbr, int nparts, const double* __restrict__ parts_dy, const double* __restrict__ iAb,
+__global__ void __launch_bounds__(PCG_THREADS) pcg_xrz_blk_kernel(long long nbr, int nparts, const double* __restrict__ parts_dy, const double* __restrict__ iAb,
                                    const double* __restrict__ d, const double* __restrict__ y, double* __restrict__ x, double* __restrict__ r,
                                    double* __restrict__ z, double* __restrict__ parts_rr, double* __restrict__ parts_rz, const CgState* st) {
     __shared__ double sh[32];
+    __shared__ double sr[PCG_THREADS * F];
     if (st->done) return;
     double dy = reduce_partials(parts_dy, nparts, sh);
     double alpha = st->rho / dy;
     double rr = 0.0, rz = 0.0;
-    for (long long br = blockIdx.x * (long long)blockDim.x + threadIdx.x; br < nbr; br += (long long)gridDim.x * blockDim.x) {
-        double ri[F];
+    const long long n = nbr * F, chunk = (long long)PCG_THREADS * F;
+    for (long long base = blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
 #pragma unroll
-        for (int a = 0; a < F; a++) {
-            const long long i = br * F + a;
-            x[i] = x[i] + alpha * d[i];
-            ri[a] = r[i] - alpha * y[i];
-            r[i] = ri[a];
+        for (int j = 0; j < F; j++) {
+            const int le = j * PCG_THREADS + threadIdx.x; const long long e = base + le;
+            if (e < n) { x[e] = x[e] + alpha * d[e]; const double ri = r[e] - alpha * y[e]; r[e] = ri; sr[le] = ri; }
         }
+        __syncthreads();
 #pragma unroll
-        for (int a = 0; a < F; a++) {
-            double zi = 0.0;
+        for (int j = 0; j < F; j++) {
+            const int le = j * PCG_THREADS + threadIdx.x; const long long e = base + le;
+            if (e < n) {
+                const int fb = (le / F) * F;
+                double zi = 0.0;
 #pragma unroll
-            for (int c = 0; c < F; c++) zi += iAb[br * (F * F) + a * F + c] * ri[c];
-            z[br * F + a] = zi;
-            rr += ri[a] * ri[a]; rz += ri[a] * zi;
+                for (int c = 0; c < F; c++) zi += iAb[e * F + c] * sr[fb + c];
+                z[e] = zi;
+                const double ri = sr[le];
+                rr += ri * ri; rz += ri * zi;
+            }
         }
+        __syncthreads();
     }
     double t = block_reduce_sum(rr, sh); if (threadIdx.x == 0) parts_rr[blockIdx.x] = t;
     t = block_reduce_sum(rz, sh); if (threadIdx.x == 0) parts_rz[blockIdx.x] = t;

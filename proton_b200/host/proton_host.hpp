@@ -121,7 +121,7 @@ template <typename T>
 class assembler {
     const cartesian_mesh<T>& msh_;
     hho_degree_info di_;
-    bool assembled_ = false;
+    bool assembled_ = false; int problem_ = PB_PROBLEM_HHO;
 public:
     sparse_matrix<T> LHS;
     std::vector<T> RHS;
@@ -134,7 +134,7 @@ public:
         p.cell_degree = (int)di_.cell_degree(); p.face_degree = (int)di_.face_degree(); p.stab_kind = stab_kind; p.problem = problem;
         p.fun = fun; p.rhs_degree_increase = rhs_degree_increase; p.eta = eta; p.keep_local = keep_local ? 1 : 0;
         msh_.check(pb_assemble(msh_.ctx(), &p));
-        assembled_ = true;
+        assembled_ = true; problem_ = problem;
     }
     // finalize(): hho.hpp:451-455 — here only the copy of the device CSR to the public members (optional: the solve
     // runs on the device-resident system)
@@ -154,7 +154,12 @@ public:
     // take_local_data for all cells at once: the reference's full solution vector (cell dofs, then face dofs)
     std::vector<T> expand_solution(size_t cbs) const {
         long long n = 0; msh_.check(pb_system_sizes(msh_.ctx(), &n, nullptr, nullptr, nullptr));
-        std::vector<T> full(msh_.num_cells() * cbs + (size_t)n);
+        size_t cell_sets = msh_.num_cells();
+        if (problem_ == PB_PROBLEM_INTERFACE) {          // cut cells carry two sets of cell unknowns (cell_table, cuthho_square.cpp:1143-1151)
+            long long ncut = 0; msh_.check(pb_cut_download(msh_.ctx(), nullptr, nullptr, nullptr, nullptr, &ncut, nullptr, nullptr));
+            cell_sets += (size_t)ncut;
+        }
+        std::vector<T> full(cell_sets * cbs + (size_t)n);
         msh_.check(pb_recover(msh_.ctx(), full.data()));
         return full;
     }
