@@ -1,10 +1,11 @@
 // C ABI — the two-material interface problem (`cuthho_square -i`): cut cells by K2i (pb_interface.cuh), uncut
 // cells by K1, and the condensed face system in the numbering of interface_assembler (apps/cuthho/cuthho_square.cpp:1091-
 // 1436): every cut face carries two sets of unknowns, face_table counts them in face order (:1161-1175), the second set
-// of face f sits fbs after the first (:1301).  First version of this row: the global matrix is built the way the reference
-// builds it (one triplet per local entry, sorted and summed — setFromTriplets, :1430-1434) with cub on the device, and the
-// solve runs on the scalar-CSR SpMV; the closed-form block structure of the plain problems does not hold around cut faces.
-// Whole-mesh contexts only.
+// of face f sits fbs after the first (:1301).  The rows of faces between two uncut cells keep the closed-form block rows of
+// the plain problems (renumbered by face_table) and are served by K3 and the block SpMV; the rows of the cut cells' faces
+// are built the way the reference builds everything (one triplet per local entry, sorted and summed — setFromTriplets,
+// :1430-1434) with cub on the device.  build_interface_system_sorted is the first version, which sorted every local entry;
+// PB_IFC_SORT_ALL=1 still selects it (comparison runs, tests).  Whole-mesh contexts only.
 
 // weight of every face in face_table: 0 Dirichlet, 2 cut, 1 otherwise
 __global__ void ifc_face_weight_kernel(Grid g, const int* __restrict__ face_loc, int* __restrict__ w) {
