@@ -130,6 +130,7 @@ static pb_status launch_interface_cut(pb_ctx* ctx, const pb_assembly_params* p, 
 // condensed system in interface_assembler's numbering: triplets -> radix sort -> sum of duplicates -> CSR
 static pb_status build_interface_system_sorted(pb_ctx* ctx) {
     const Grid& g = ctx->grid; const int F = ctx->F, NF = ctx->NF;
+    ctx->ifc_struct_ok = false; dfree(&ctx->brows); dfree(&ctx->brp);          // no block-row table on this path: pb_pcg takes the scalar-CSR SpMV
     const long long nc = g.Nx * g.Ny, nf = ctx->nfaces;
     cudaStream_t sm = ctx->stream;
     int* w = nullptr; CK(cudaMalloc((void**)&w, (size_t)(nf + 1) * 4));
@@ -204,11 +205,12 @@ static pb_status build_interface_system_sorted(pb_ctx* ctx) {
 // four faces, both sets of the cut ones; about 4 ncut block rows) are built from sorted triplets.  All rows still come in
 // groups of fbs with fbs-wide column blocks, so one brp / rowptr layout covers both kinds.
 
-__global__ void ifc_flag_irregular_kernel(Grid g, int ncut, const int* __restrict__ cut_cells, int* __restrict__ irr) {
+// irr[nfaces] (one past the faces) counts the Dirichlet faces met on cut cells: the reference refuses them (:1292-1293)
+__global__ void ifc_flag_irregular_kernel(Grid g, int ncut, const int* __restrict__ cut_cells, int* __restrict__ irr, long long nfaces) {
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < ncut; s += gridDim.x * blockDim.x) {
         const long long c = cut_cells[s], ci = c % g.Nx, cj = c / g.Nx;
         long long f[4]; cell_faces(g, ci, cj, f);
-        for (int li = 0; li < 4; li++) if (!cell_face_dirichlet(g, ci, cj, li)) irr[f[li]] = 1;
+        for (int li = 0; li < 4; li++) { if (!cell_face_dirichlet(g, ci, cj, li)) irr[f[li]] = 1; else atomicAdd(irr + nfaces, 1); }
     }
 }
 // face id -> the two cells of a free face and the local index of the face in each (as build_block_rows_kernel)
@@ -408,7 +410,7 @@ static pb_status build_interface_system(pb_ctx* ctx) {
         IFC(dalloc(ctx, &ctx->irr_faces, (size_t)nf + 1));
         IFC(cudaMemsetAsync(w, 0, (size_t)(nf + 1) * 4, sm)); IFC(cudaMemsetAsync(irr, 0, (size_t)(nf + 1) * 4, sm));
         ifc_face_weight_kernel<<<148 * 8, 256, 0, sm>>>(g, ctx->face_loc, w);
-        if (ctx->ncut > 0) ifc_flag_irregular_kernel<<<(ctx->ncut + 255) / 256, 256, 0, sm>>>(g, ctx->ncut, ctx->cut_cells, irr);
+        if (ctx->ncut > 0) ifc_flag_irregular_kernel<<<(ctx->ncut + 255) / 256, 256, 0, sm>>>(g, ctx->ncut, ctx->cut_cells, irr, nf);
         IFC(dalloc(ctx, &ctx->ftab, (size_t)nf + 1));
         size_t tb = 0;
         IFC(cub::DeviceScan::ExclusiveSum(nullptr, tb, w, ctx->ftab, (int)(nf + 1), sm));
@@ -418,11 +420,13 @@ static pb_status build_interface_system(pb_ctx* ctx) {
         IFC(cub::DeviceSelect::Flagged(nullptr, tb, cub::CountingInputIterator<int>(0), irr, ctx->irr_faces, dcount, (int)nf, sm));
         IFC(cudaMalloc(&tmp, tb));
         IFC(cub::DeviceSelect::Flagged(tmp, tb, cub::CountingInputIterator<int>(0), irr, ctx->irr_faces, dcount, (int)nf, sm));
-        int nslots = 0, nirr = 0;
+        int nslots = 0, nirr = 0, ndir_cut = 0;
         IFC(cudaMemcpyAsync(&nslots, ctx->ftab + nf, 4, cudaMemcpyDeviceToHost, sm));
         IFC(cudaMemcpyAsync(&nirr, dcount, 4, cudaMemcpyDeviceToHost, sm));
+        IFC(cudaMemcpyAsync(&ndir_cut, irr + nf, 4, cudaMemcpyDeviceToHost, sm));
         IFC(cudaStreamSynchronize(sm));
         cudaFree(tmp); tmp = nullptr;
+        if (ndir_cut > 0) { release(); return fail(ctx, PB_ERR_INVALID, "Dirichlet boundary on cut cell not supported."); }      // interface_assembler::assemble_cut, :1292-1293
         const long long n = (long long)nslots * F;
         if (n >= (1ll << 31)) { release(); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: interface system too large for 32-bit column indices"); }
         ctx->nrows = n; ctx->nrows_blk = nslots; ctx->n_irr_faces = nirr;

@@ -168,3 +168,13 @@ def test_interface_full_size_properties():
         assert res["iterations"] >= 50 and np.all(np.isfinite(c.face_solution()))
     finally:
         c.close()
+
+
+def test_interface_refuses_cut_cells_on_the_dirichlet_boundary(ctx):
+    """interface_assembler::assemble_cut throws "Dirichlet boundary on cut cell not supported." (cuthho_square.cpp:1292-1293)"""
+    N, k = 12, 1
+    ctx.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT)
+    ctx.cut_levelset(0, 0.48, 0.5, 0.5)          # the circle reaches into the boundary cells
+    ctx.cut_preprocess(4)
+    with pytest.raises(pb.ProtonError, match="Dirichlet boundary on cut cell"):
+        ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
