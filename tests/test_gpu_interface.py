@@ -82,6 +82,10 @@ def test_interface_condensed_system_and_solve(ctx, k, N):
     assert res["exit_reason"] == PB.CG_CONVERGED
     x = ctx.face_solution()
     assert frob_rel(x, sol[nT:]) < 1e-8
+    if k >= 1:      # the block-Jacobi extension on the interface numbering (cut faces: two blocks each)
+        rb = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, 2))
+        assert rb["exit_reason"] == PB.CG_CONVERGED and frob_rel(ctx.face_solution(), sol[nT:]) < 1e-8
+        ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, True))
     # back-substitution on the device, in the layout of the reference's solution vector (cell_table: cut cells twice)
     full = ctx.recover()
     assert full.shape == sol.shape and frob_rel(full, sol) < 1e-8
