@@ -213,7 +213,8 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     // memory), so a batch of `check_every` iterations is captured once into a CUDA graph and replayed; the host only
     // polls the state between batches.  Multi-rank runs keep plain launches (NCCL calls between the kernels).
     cudaGraph_t graph = nullptr; cudaGraphExec_t gexec = nullptr;
-    if (!multi && !getenv("PB_PCG_NO_GRAPH")) {
+    // (PB_PCG_GRAPH_MULTI=1: capture the multi-rank iteration too — NCCL's send/recv and all-reduces are capturable; opt-in)
+    if ((!multi || getenv("PB_PCG_GRAPH_MULTI")) && !getenv("PB_PCG_NO_GRAPH")) {
         CK(cudaStreamBeginCapture(sm, cudaStreamCaptureModeThreadLocal));
         pb_status cst = PB_OK;
         for (int k = 0; k < check_every && cst == PB_OK; k++) cst = full_iteration();
