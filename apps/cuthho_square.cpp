@@ -41,6 +41,7 @@ int main(int argc, char** argv) {
             std::cout << "CG iterations: " << iters << (er == pb::cg_exit_reason::CONVERGED ? "" : " (NOT CONVERGED)") << std::endl;
             auto e = assembler.error_norms();
             printf("Energy-norm absolute error:           %.10e\n", std::sqrt(e[0]));                  // :1837
+            assembler.write_solution("interface_uT.dat");                                                // uT_gp, :1795-1796, 1839-1842
         } catch (const std::exception& ex) { std::cerr << ex.what() << std::endl; return 2; }
     }
     if (!solve_fictdom) return 0;

@@ -180,7 +180,8 @@ pb_status pb_interface_face_table(pb_ctx* ctx, long long* table);
  * updates, the closing line included, iterations + 2 entries in all; capacity 0 switches it off.
  * pb_sample_solution: the rows "x y value" of the driver's solution_N_<N>_k_<k>.dat (convergence_test.cpp:250-252,
  * 280-286) for the owned cells: cell solution at the degree-2*cell_degree quadrature points, cells ascending, points in
- * integrate()'s order; xyv = 3 doubles per point (NULL: only *n_points is set). ---- */
+ * integrate()'s order; xyv = 3 doubles per point (NULL: only *n_points is set).  On the interface problem: the rows of
+ * interface_uT.dat (cuthho_square.cpp:1775-1833): cut cells contribute their negative, then their positive part. ---- */
 pb_status pb_pcg_history(pb_ctx* ctx, long long capacity);
 pb_status pb_pcg_get_history(pb_ctx* ctx, double* out, long long capacity, long long* n);
 pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points);

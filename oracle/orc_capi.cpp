@@ -134,7 +134,7 @@ long long orc_cell_quadrature(void* h, long long cell, int degree, int kind, int
     ORC_TRY
     auto* H = (MeshH*)h; const Cell& cl = H->m.cells.at(cell);
     std::vector<QP> q = (kind == 1) ? integrate_interface(H->m, cl, degree, IN_NEGATIVE_SIDE)
-                        : (where_aware ? integrate_where(H->m, cl, degree, IN_NEGATIVE_SIDE) : integrate(H->m, cl, degree));
+                        : (where_aware ? integrate_where(H->m, cl, degree, where_aware == 2 ? IN_POSITIVE_SIDE : IN_NEGATIVE_SIDE) : integrate(H->m, cl, degree));   /* where_aware: 1 negative part, 2 positive part */
     if (pts) for (size_t i = 0; i < q.size(); i++) { pts[2 * i] = q[i].first.x; pts[2 * i + 1] = q[i].first.y; w[i] = q[i].second; }
     return (long long)q.size();
     ORC_CATCH(-1)

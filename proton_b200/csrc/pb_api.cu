@@ -637,6 +637,7 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
 
 static pb_status interface_recover(pb_ctx* ctx, double* full);
 static pb_status interface_error(pb_ctx* ctx, double out[3]);
+static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points);
 #include "pb_api_dist.inl"
 #include "pb_api_interface_post.inl"
 #include "pb_api_obstacle.inl"

@@ -318,7 +318,8 @@ static cudaError_t launch_norms_t(pb_ctx* c, NormArgs& A, int grid) {
 extern "C" pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && n_points, PB_ERR_STATE, "pb_sample_solution: no face solution");
-    NEED(ctx->prm.problem == PB_PROBLEM_HHO && !ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_sample_solution: uncut HHO problems only");
+    if (ctx->general_csr) { CK(cudaSetDevice(ctx->device)); return interface_sample(ctx, xyv, capacity_points, n_points); }      // interface_uT.dat
+    NEED(ctx->prm.problem == PB_PROBLEM_HHO, PB_ERR_UNSUPPORTED, "pb_sample_solution: uncut HHO and interface problems only");
     CK(cudaSetDevice(ctx->device));
     const int cd = ctx->CD, qk = ctx->quad_kind;
     NEED(cd >= 0 && cd <= 4, PB_ERR_UNSUPPORTED, "pb_sample_solution: cell degree > 4");

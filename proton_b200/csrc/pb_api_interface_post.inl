@@ -124,6 +124,113 @@ __global__ void __launch_bounds__(32) interface_h1_kernel(Grid g, const double2*
     if (lane == 0) parts[blockIdx.x] = sum;
 }
 
+static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** ucut_out);
+// rows "x y u_T" of the driver's interface_uT.dat (cuthho_square.cpp:1775-1833, gnuplot_output_object :754-780): cells in
+// order, uncut cells over integrate(msh, cl, 2 cd), cut cells over the negative then the positive part.  A cut cell always has
+// (4 + 2 NI) * np points (every vertex lies on exactly one side), so the row offsets are closed forms.  One warp per cell.
+template <int CD>
+__global__ void __launch_bounds__(32) interface_sample_kernel(Grid g, const double2* __restrict__ points, const int* __restrict__ node_loc,
+                                                               const int* __restrict__ cell_loc, const int* __restrict__ cut_cells, const double2* __restrict__ iface,
+                                                               int ncut, int NI, const double* __restrict__ uc, const double* __restrict__ ucut, double* __restrict__ out) {
+    constexpr int C = cell_basis_size(CD);
+    constexpr int nq0 = cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * CD);
+    __shared__ double tp[2 * CUT_MAX_TP];
+    __shared__ int s_ntp;
+    const int lane = threadIdx.x;
+    const long long nc = g.Nx * g.Ny;
+    const int ri = dunavant_rule_index(2 * CD), np = c_qt.dun_n[ri];
+    const long long ncutq = (long long)(4 + 2 * NI) * np;
+    for (long long c = blockIdx.x; c < nc; c += gridDim.x) {
+        const long long ci = c % g.Nx, cj = c / g.Nx, p0 = grid_point(g, ci, cj);
+        const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
+        CellGeom geo; int nloc[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const double2 v = points[pid[i]]; geo.vx[i] = v.x; geo.vy[i] = v.y; nloc[i] = node_loc[pid[i]]; }
+        cell_geometry(geo);
+        const double ih = geo.ihalf;
+        int lo = 0, hi = ncut;                      // cut cells before c
+        while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
+        double* o = out + 3 * ((c - lo) * nq0 + lo * ncutq);
+        auto emit = [&](const double* u, long long idx, double x, double y) {
+            double phi[C], dx[C], dy[C];
+            eval_cell_basis<CD>((x - geo.barx) * ih, (y - geo.bary) * ih, ih, phi, dx, dy);
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < C; i++) v += u[i] * phi[i];
+            o[3 * idx] = x; o[3 * idx + 1] = y; o[3 * idx + 2] = v;
+        };
+        if (cell_loc[c] != PB_ON_INTERFACE) {
+            for (int q = lane; q < nq0; q += 32) { double x, y, w; cell_qp<PB_QUAD_POLY_DUNAVANT, 2 * CD>(geo, q, x, y, w); emit(uc + c * C, q, x, y); }
+        } else {
+            const double2* I = iface + (long long)lo * NI;
+            long long done = 0;
+            for (int sd = 0; sd < 2; sd++) {
+                const int WHERE = sd == 0 ? PB_IN_NEGATIVE_SIDE : PB_IN_POSITIVE_SIDE;
+                __syncwarp();
+                if (lane == 0) {
+                    int n = 0;
+                    auto push = [&](double x, double y) { tp[2 * n] = x; tp[2 * n + 1] = y; n++; };
+                    auto push_iface = [&]() {
+                        if (sd == 0) for (int i = 0; i < NI; i++) push(I[i].x, I[i].y);
+                        else for (int i = NI - 1; i >= 0; i--) push(I[i].x, I[i].y);
+                    };
+                    const bool c1 = nloc[0] == WHERE && nloc[3] != WHERE, c2 = nloc[0] != WHERE && nloc[3] == WHERE, c3 = nloc[0] != WHERE && nloc[3] != WHERE;
+                    if (c1 || c2 || c3) { for (int i = 0; i < 4; i++) if (nloc[i] == WHERE) push(sel4(geo.vx, i), sel4(geo.vy, i)); push_iface(); }
+                    else {
+                        int i = 0;
+                        while (i < 4 && nloc[i] == WHERE) { push(sel4(geo.vx, i), sel4(geo.vy, i)); i++; }
+                        push_iface();
+                        while (i < 4 && nloc[i] != WHERE) i++;
+                        while (i < 4 && nloc[i] == WHERE) { push(sel4(geo.vx, i), sel4(geo.vy, i)); i++; }
+                    }
+                    s_ntp = n;
+                }
+                __syncwarp();
+                const int ntp = s_ntp;
+                double rx = 0, ry = 0, den = 0; const double x0 = tp[0], y0 = tp[1];
+                for (int i = 2; i < ntp; i++) {
+                    const double ax = tp[2 * (i - 1)] - x0, ay = tp[2 * (i - 1) + 1] - y0, bx = tp[2 * i] - x0, by = tp[2 * i + 1] - y0;
+                    const double d = (ax * by - ay * bx) / 2.0; rx += (ax + bx) * d; ry += (ay + by) * d; den += d;
+                }
+                const double pbx = x0 + rx / (den * 3), pby = y0 + ry / (den * 3);
+                const int nq = ntp * np;
+                for (int q = lane; q < nq; q += 32) {
+                    const int t = q / np, p = q - t * np, t1 = (t + 1) % ntp;
+                    const double ax = tp[2 * t], ay = tp[2 * t + 1], bx = tp[2 * t1], by = tp[2 * t1 + 1];
+                    const double* row = c_qt.dun[ri][p];
+                    emit(ucut + (long long)lo * 2 * C + sd * C, done + q, pbx * row[0] + ax * row[1] + bx * row[2], pby * row[0] + ay * row[1] + by * row[2]);
+                }
+                done += nq;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
+    const Grid& g = ctx->grid; const int CD = ctx->CD;
+    const long long nc = g.Nx * g.Ny;
+    const int np = dunavant_npts(2 * CD);
+    const long long nq0 = cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * CD), ncutq = (long long)(4 + 2 * ctx->NI) * np;
+    const long long total = (nc - ctx->ncut) * nq0 + (long long)ctx->ncut * ncutq;
+    *n_points = total;
+    if (!xyv) return PB_OK;
+    NEED(capacity_points >= total, PB_ERR_INVALID, "pb_sample_solution: buffer too small");
+    double *uc = nullptr, *ucut = nullptr, *out = nullptr;
+    pb_status st = interface_cell_unknowns(ctx, &uc, &ucut); if (st != PB_OK) return st;
+    CK(cudaMalloc((void**)&out, (size_t)total * 24));
+    const int grid = (int)std::min<long long>(nc, 148 * 32);
+#define PB_SMP(CD_) interface_sample_kernel<CD_><<<grid, 32, 0, ctx->stream>>>(g, ctx->points, ctx->node_loc, ctx->cell_loc_g, ctx->cut_cells, ctx->iface, ctx->ncut, ctx->NI, uc, ucut, out)
+    switch (CD) { case 1: PB_SMP(1); break; case 2: PB_SMP(2); break; default: PB_SMP(3); break; }
+#undef PB_SMP
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xyv, out, (size_t)total * 24, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(uc); cudaFree(ucut); cudaFree(out);
+    if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_sample_solution (interface): %s", cudaGetErrorString(e));
+    return PB_OK;
+}
+
 // cell unknowns of all cells (uc: regular cell order; ucut: [u-, u+] per cut slot) from the face solution ctx->x
 static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** ucut_out) {
     const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;

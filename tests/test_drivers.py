@@ -55,6 +55,8 @@ def test_cuthho_square_interface_driver_prints_reference_error(golden, tmp_path)
     ref = golden["cuthho_interface"]["k1_N20_r4"]
     assert abs(err - ref) / ref < 1e-5
     assert (tmp_path / "cuthho_cg_hist.dat").exists()
+    rows = (tmp_path / "interface_uT.dat").read_text().splitlines()
+    assert len(rows) > 20 * 20 * 4 * 6 and len(rows[0].split()) == 3
 
 
 @pytest.mark.gpu

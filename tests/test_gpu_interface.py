@@ -182,3 +182,34 @@ def test_interface_refuses_cut_cells_on_the_dirichlet_boundary(ctx):
     ctx.cut_preprocess(4)
     with pytest.raises(pb.ProtonError, match="Dirichlet boundary on cut cell"):
         ctx.assemble(pb.hho_degree_info(k + 1, k), stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+
+
+@pytest.mark.parametrize("k,N", [(1, 10), (2, 12)])
+def test_interface_solution_samples_match_the_driver_dat_rows(ctx, k, N):
+    """pb_sample_solution on the interface problem = rows of interface_uT.dat (cuthho_square.cpp:1775-1833): oracle
+    quadrature points (uncut cells, then both parts of the cut cells: negative first), scaled monomial basis restated here,
+    cell unknowns from pb_recover (reference layout: cut cells carry [u-, u+])."""
+    m = _setup(ctx, N, k)
+    S = orc.InterfaceSystem(m, k)
+    res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 50 * ctx.n_rows, True))
+    assert res["exit_reason"] == PB.CG_CONVERGED
+    full = ctx.recover(); got = ctx.sample_solution()
+    cd = k + 1; C_ = (cd + 1) * (cd + 2) // 2
+    info = m.cut_info(); bar = m.barycenters(); h = np.hypot(1.0 / N, 1.0 / N)
+    pts_all = m.points(); cells = m.cells()[0]
+    rows = []
+    for c in range(m.ncells):
+        # cell basis: barycenter and diameter of the (possibly displaced) full cell
+        v = pts_all[cells[c]]
+        hc = max(np.linalg.norm(v[i] - v[j]) for i in range(4) for j in range(i + 1, 4))
+        parts = [(m.quadrature(c, 2 * cd)[0], 0)] if info["cell_loc"][c] != 2 else \
+                [(m.quadrature(c, 2 * cd, where_aware=1)[0], 0), (m.quadrature(c, 2 * cd, where_aware=2)[0], 1)]
+        for pts, sd in parts:
+            o = (S.cell_table[c] + sd) * C_
+            bx = (pts[:, 0] - bar[c, 0]) / (0.5 * hc); by = (pts[:, 1] - bar[c, 1]) / (0.5 * hc)
+            phi = np.stack([bx ** (d - i) * by ** i for d in range(cd + 1) for i in range(d + 1)], axis=1)
+            rows.append(np.column_stack([pts, phi @ full[o:o + C_]]))
+    want = np.vstack(rows)
+    assert got.shape == want.shape
+    assert np.max(np.abs(got[:, :2] - want[:, :2])) < 1e-13
+    assert np.max(np.abs(got[:, 2] - want[:, 2])) < 1e-11 * max(1.0, np.max(np.abs(want[:, 2])))
