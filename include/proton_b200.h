@@ -50,8 +50,10 @@ typedef struct {
 } pb_assembly_params;
 
 /* cg_params (solver_cg.hpp:44-61).  apply_preconditioner: 0 = none, 1 = the reference's diagonal preconditioner
- * (solver_cg.hpp:78-81), 2 = fbs x fbs block-Jacobi (inverse of every face's diagonal block; an extension with no
- * reference counterpart: same solution to the tolerance, fewer iterations for face degree >= 2). */
+ * (solver_cg.hpp:78-81); extensions with no reference counterpart (same solution to the tolerance, fewer iterations):
+ * 2 = fbs x fbs block-Jacobi (inverse of every face's diagonal block), 3 = multigrid V-cycle (Chebyshev/block-Jacobi
+ * smoothing on the face system, Galerkin vertex-based coarse levels; plain and fictitious-domain problems, face degree
+ * <= 3, whole meshes and strips; iteration counts independent of the mesh size on the plain problem). */
 typedef struct { double convergence_threshold, divergence_threshold; long long max_iter; int apply_preconditioner; } pb_cg_params;
 
 typedef struct { long long iterations; double relative_residual; int exit_reason; double seconds; } pb_cg_result;
@@ -166,8 +168,10 @@ pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
  * on both sides on cut cells, then interface_assembler::assemble / assemble_cut / finalize (:1197-1340, 1430-1434) onto the
  * condensed face system in interface_assembler's numbering: unknown (f, a) = face_table[f]*fbs + a, the second set of a cut
  * face fbs further (:1161-1175, 1301).  Whole-mesh contexts, HHO(k+1,k), k <= 2, kappa_1 = kappa_2 = 1 (params<T>, :293-299).
- * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems; back-substitution and the driver's H1 error
- * are not built yet.  pb_interface_get_local: per-cut-cell arrays in ascending cell order (what = 0: condensed block,
+ * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems.  pb_recover returns interface_assembler's solution
+ * layout: (ncells + ncut) cell blocks of cbs in cell_table order (a cut cell carries its negative, then its positive set,
+ * :1143-1160), then the face unknowns; pb_error_norms out[0] = the driver's H1 error^2 over both parts (:1775-1833);
+ * pb_sample_solution the rows of interface_uT.dat.  pb_interface_get_local: per-cut-cell arrays in ascending cell order (what = 0: condensed block,
  * (8 fbs)^2 column-major in the driver's local order [faces-, faces+]; 1: condensed rhs; with keep_local 2: the local matrix
  * (2 cbs + 8 fbs)^2 in the order [cell-, cell+, faces-, faces+]; 3: the local load, 2 cbs).  pb_interface_face_table:
  * face_table per face, -1 for Dirichlet faces. ---- */
@@ -185,6 +189,17 @@ pb_status pb_interface_face_table(pb_ctx* ctx, long long* table);
 pb_status pb_pcg_history(pb_ctx* ctx, long long capacity);
 pb_status pb_pcg_get_history(pb_ctx* ctx, double* out, long long capacity, long long* n);
 pb_status pb_sample_solution(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points);
+
+/* ---- multigrid preconditioner (apply_preconditioner = 3), inspection for tests and bench; no reference counterpart.
+ * pb_mg_info builds the hierarchy for the current system if needed: number of vertex levels, the upper end of the smoothing
+ * range (1.1 x the power-iteration estimate of lambda_max(D^-1 A)), milliseconds this call spent building (0 when cached).
+ * pb_mg_level: dims = { Nx, Ny, first stored vertex row, stored vertex rows, first stored cell row, stored cell rows };
+ * stencil9 (may be NULL): 9 x stored vertices, entry k = (dj+1)*3 + di+1 of vertex v at [k * nvertices + v];
+ * elements16 (may be NULL): 4 x 4 Galerkin element matrix per stored cell, row-major, corners (i,j) (i+1,j) (i+1,j+1) (i,j+1).
+ * pb_mg_apply: z = M^-1 r for host vectors of the owned rows (all ranks of a communicator call it together). ---- */
+pb_status pb_mg_info(pb_ctx* ctx, int* n_levels, double* lmax, double* setup_ms);
+pb_status pb_mg_level(pb_ctx* ctx, int level, long long dims[6], double* stencil9, double* elements16);
+pb_status pb_mg_apply(pb_ctx* ctx, const double* r, double* z);
 
 /* ---- measurement hooks (bench.py): device-side timing of the last pb_assemble / pb_pcg, milliseconds ---- */
 pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg);

@@ -73,6 +73,9 @@ def lib():
         L.pb_pcg_history.argtypes = [C.c_void_p, C.c_longlong]
         L.pb_pcg_get_history.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
         L.pb_sample_solution.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
+        L.pb_mg_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pb_mg_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pb_mg_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -273,6 +276,28 @@ class Context:
         r = _CgResult()
         self._ck(lib().pb_pcg(self._h, C.byref(p), C.byref(r)))
         return dict(iterations=r.iterations, relative_residual=r.relative_residual, exit_reason=r.exit_reason, seconds=r.seconds)
+
+    # ---- multigrid preconditioner (apply_preconditioner = 3)
+    def mg_info(self):
+        """builds the hierarchy for the current system if needed: (vertex levels, upper end of the smoothing range, setup ms)"""
+        nl = C.c_int(); lm = C.c_double(); ms = C.c_double()
+        self._ck(lib().pb_mg_info(self._h, C.byref(nl), C.byref(lm), C.byref(ms)))
+        return nl.value, lm.value, ms.value
+
+    def mg_level(self, level, stencil=True, elements=False):
+        d = (C.c_longlong * 6)()
+        self._ck(lib().pb_mg_level(self._h, int(level), d, None, None))
+        Nx, Ny, row0, nrows, crow0, ncrows = [int(v) for v in d]
+        st = np.zeros((9, nrows * (Nx + 1))) if stencil else None
+        el = np.zeros((ncrows * Nx, 16)) if elements else None
+        self._ck(lib().pb_mg_level(self._h, int(level), d, _ptr(st), _ptr(el)))
+        return dict(Nx=Nx, Ny=Ny, row0=row0, nrows=nrows, crow0=crow0, ncrows=ncrows, stencil=None if st is None else st.T.copy(), elements=el)
+
+    def mg_apply(self, r):
+        r = np.ascontiguousarray(r, np.float64); assert r.shape == (self.n_rows,)
+        z = np.zeros(self.n_rows)
+        self._ck(lib().pb_mg_apply(self._h, _ptr(r), _ptr(z)))
+        return z
 
     # ---- interface problem (SURVEY 8f.3)
     def interface_local(self, what):

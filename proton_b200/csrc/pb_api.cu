@@ -19,6 +19,7 @@
 #include "pb_interface.cuh"
 #include "pb_norms.cuh"
 #include "pb_pcg.cuh"
+#include "pb_mg.cuh"
 #include "pb_system.cuh"
 #include "pb_generic.cuh"
 #include "pb_obstacle.cuh"
@@ -61,6 +62,9 @@ struct pb_ctx {
     double *x = nullptr, *r = nullptr, *z = nullptr, *d = nullptr, *y = nullptr, *iA = nullptr, *iAb = nullptr, *parts = nullptr;
     CgState* cg = nullptr;
     double *dfull = nullptr, *scal = nullptr;      // d with halos (d = dfull + halo_lo); all-reduced scalars
+    long long solver_n = -1, solver_nfull = -1, iAb_n = -1;      // sizes the solver vectors / iAb were allocated for
+    long long asm_gen = 0;                          // bumped whenever the system values change (multigrid setup cache)
+    MgState mg;                                     // multigrid preconditioner (pb_api_mg.inl)
     // obstacle active-set state (per cell)
     double *ob_alpha = nullptr, *ob_beta = nullptr, *ob_gamma = nullptr, *ob_xprev = nullptr; unsigned char* ob_inA = nullptr; bool ob_ready = false;
     // multi-GPU
@@ -159,12 +163,18 @@ extern "C" pb_status pb_ctx_create(int device, pb_ctx** out) {
     *out = ctx; return PB_OK;
 }
 
+static void mg_free(pb_ctx* c);      // pb_api_mg.inl
+static void free_solver(pb_ctx* c) {
+    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->iAb); dfree(&c->parts); dfree(&c->scal);
+    c->solver_n = c->solver_nfull = c->iAb_n = -1;
+    mg_free(c);
+}
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
     dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); dfree(&c->irr_rows); c->n_irr_rows = 0; dfree(&c->irr_faces); c->n_irr_faces = 0; c->ifc_struct_ok = false;
     dfree(&c->ifc_k0); dfree(&c->ifc_k1); dfree(&c->ifc_v0); dfree(&c->ifc_v1); dfree(&c->ifc_dnum); if (c->ifc_tmp) { cudaFree(c->ifc_tmp); c->ifc_tmp = nullptr; } c->ifc_T = 0; c->ifc_ncut_alloc = 0; c->general_csr = false;
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
-    dfree(&c->x); dfree(&c->r); dfree(&c->z); dfree(&c->dfull); c->d = nullptr; dfree(&c->y); dfree(&c->iA); dfree(&c->iAb); dfree(&c->parts); dfree(&c->scal);
+    free_solver(c);
     dfree(&c->ob_alpha); dfree(&c->ob_beta); dfree(&c->ob_gamma); dfree(&c->ob_xprev); dfree(&c->ob_inA); c->ob_ready = false;
     c->assembled = false;
 }
@@ -488,7 +498,7 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
         ctx->out_pending = true;
     }
     ctx->pipe_in_flight = !sync; ctx->step_timed = true;
-    ctx->assembled = true;
+    ctx->assembled = true; ctx->asm_gen++;
     if (sync) return pb_pipeline_sync(ctx);
     return PB_OK;
 }
@@ -561,9 +571,10 @@ extern "C" pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, l
 }
 
 // ------------------------------------------------------------------------------------------------ stage 3
+static pb_status ensure_solver(pb_ctx* ctx);      // pb_api_dist.inl
 extern "C" pb_status pb_get_face_solution(pb_ctx* ctx, double* x) {
     if (!ctx) return PB_ERR_INVALID;
-    NEED(ctx->assembled && ctx->x && x, PB_ERR_STATE, "pb_get_face_solution: no solution");
+    NEED(ctx->assembled && ctx->x && x && ctx->solver_n == ctx->nrows, PB_ERR_STATE, "pb_get_face_solution: no solution");
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemcpy(x, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost)); return PB_OK;
 }
@@ -571,7 +582,7 @@ extern "C" pb_status pb_set_face_solution(pb_ctx* ctx, const double* x) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && x, PB_ERR_STATE, "pb_set_face_solution: nothing assembled");
     CK(cudaSetDevice(ctx->device));
-    if (!ctx->x) CK(dalloc(ctx, &ctx->x, (size_t)ctx->nrows));
+    { pb_status st = ensure_solver(ctx); if (st != PB_OK) return st; }
     CK(cudaMemcpy(ctx->x, x, (size_t)ctx->nrows * 8, cudaMemcpyHostToDevice)); return PB_OK;
 }
 
@@ -639,6 +650,7 @@ static pb_status interface_recover(pb_ctx* ctx, double* full);
 static pb_status interface_error(pb_ctx* ctx, double out[3]);
 static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points);
 #include "pb_api_dist.inl"
+#include "pb_api_mg.inl"
 #include "pb_api_interface_post.inl"
 #include "pb_api_obstacle.inl"
 

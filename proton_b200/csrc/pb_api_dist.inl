@@ -110,6 +110,76 @@ template <int F> static int spmv_blk_blocks_per_sm() {
 }
 static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 ? 8 : len <= 24 ? 8 : 16; }
 
+// ---- solver workspace: every vector of the Krylov solvers is (re)allocated together whenever the system size differs
+// from the size they were made for (pb_set_face_solution on a fresh assembly, a re-assembled interface system with
+// another cut, ...), so no entry point can run on a partly allocated or stale-sized set
+static pb_status ensure_solver(pb_ctx* ctx) {
+    const long long n = ctx->nrows; const int F = ctx->F;
+    const long long nfull = ctx->general_csr ? n : (ctx->strip.col_hi - ctx->strip.col_lo) * F;      // interface problem: whole mesh, its own numbering
+    const bool ok = ctx->solver_n == n && ctx->solver_nfull == nfull && ctx->x && ctx->r && ctx->z && ctx->dfull && ctx->y && ctx->iA && ctx->parts && ctx->scal;
+    if (!ok) {
+        free_solver(ctx);
+        CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
+        CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
+        CK(dalloc(ctx, &ctx->parts, (size_t)4 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
+        CK(cudaMemsetAsync(ctx->dfull, 0, (size_t)nfull * 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->x, 0, (size_t)n * 8, ctx->stream));
+        ctx->solver_n = n; ctx->solver_nfull = nfull;
+    }
+    ctx->d = ctx->dfull + (ctx->general_csr ? 0 : (ctx->strip.cf_begin - ctx->strip.col_lo) * F);
+    return PB_OK;
+}
+static pb_status ensure_block_inverse(pb_ctx* ctx) {
+    const long long want = ctx->nrows * ctx->F;
+    if (!ctx->iAb || ctx->iAb_n != want) { CK(dalloc(ctx, &ctx->iAb, (size_t)want)); ctx->iAb_n = want; }
+    return PB_OK;
+}
+
+// ---- y = A v on the owned rows (v with halos), with the partial sums of v.y: which kernel, which grid
+struct SpmvPlan {
+    long long n, xoff, down; int F, lpr, nblk, nblk_sp, nblk_irr; bool use_csr;
+    int ndy() const { return nblk_sp + nblk_irr; }      // number of d.y partials
+};
+static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
+    SpmvPlan P{};
+    const int F = ctx->F; const long long n = ctx->nrows;
+    P.n = n; P.F = F; P.xoff = ctx->general_csr ? 0 : ctx->strip.col_lo * F; P.down = ctx->general_csr ? 0 : (ctx->strip.cf_begin - ctx->strip.col_lo) * F;
+    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
+    int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
+    const long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
+    P.nblk = nblk; P.lpr = spmv_lanes(F);
+    // scalar CSR: comparison runs, F = 1 (a 64-byte face record per row costs more than 7 column indices) and F > 4
+    P.use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || (ctx->general_csr && !ctx->ifc_struct_ok);
+    // interface problem: block kernel on the block rows in interface order + a scalar pass over the rows of the cut cells' faces
+    P.nblk_irr = (!P.use_csr && ctx->general_csr && ctx->n_irr_rows > 0) ? (int)std::min<long long>(PCG_MAX_BLOCKS, ((long long)ctx->n_irr_rows * F + 7) / 8) : 0;
+    P.nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
+    if (!P.use_csr) {
+        const int occ = F == 1 ? spmv_blk_blocks_per_sm<1>() : F == 2 ? spmv_blk_blocks_per_sm<2>() : F == 3 ? spmv_blk_blocks_per_sm<3>() : spmv_blk_blocks_per_sm<4>();
+        P.nblk_sp = nsm * occ; if (P.nblk_sp > PCG_MAX_BLOCKS) P.nblk_sp = PCG_MAX_BLOCKS;
+        const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < P.nblk_sp) P.nblk_sp = (int)(wantg < 1 ? 1 : wantg);
+    }
+    return P;
+}
+static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull, double* y, double* p_dy) {
+    cudaStream_t sm = ctx->stream; const long long n = P.n; const int F = P.F;
+#define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<P.nblk_sp, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->brows, ctx->brp, ctx->val, vfull, P.down, y, p_dy, ctx->cg)
+    if (P.use_csr) {
+        switch (P.lpr) {
+        case 4: pcg_spmv_kernel<4><<<P.nblk, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->rowptr, ctx->col, ctx->val, vfull, P.down, y, p_dy, ctx->cg); break;
+        case 8: pcg_spmv_kernel<8><<<P.nblk, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->rowptr, ctx->col, ctx->val, vfull, P.down, y, p_dy, ctx->cg); break;
+        default: pcg_spmv_kernel<16><<<P.nblk, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->rowptr, ctx->col, ctx->val, vfull, P.down, y, p_dy, ctx->cg); break;
+        }
+    } else {
+        switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
+    }
+#undef PB_SPMV
+    if (P.nblk_irr) pcg_spmv_rows_kernel<<<P.nblk_irr, PCG_THREADS, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rowptr, ctx->col, ctx->val, vfull, y, p_dy + P.nblk_sp, ctx->cg);
+    CK(cudaGetLastError());
+    return PB_OK;
+}
+
+static pb_status pcg_multigrid(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res);      // pb_api_mg.inl
+
 // conjugated_gradient (solver_cg.hpp:63-144) on the condensed system of this context, or of the row of contexts that
 // share a communicator: same update order, exit tests and iteration count; dot products are all-reduced.
 extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res) {
@@ -118,21 +188,14 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     DRAIN();
     const bool whole = ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid);
     NEED(whole || (ctx->world > 1 && ctx->comm), PB_ERR_STATE, "pb_pcg: this context owns a strip: call pb_dist_init on every rank first");
+    NEED(p->apply_preconditioner >= 0 && p->apply_preconditioner <= 3, PB_ERR_INVALID, "pb_pcg: apply_preconditioner must be 0 (none), 1 (diagonal), 2 (block-Jacobi) or 3 (multigrid)");
     CK(cudaSetDevice(ctx->device));
+    { pb_status st = ensure_solver(ctx); if (st != PB_OK) return st; }
+    if (p->apply_preconditioner == 3) return pcg_multigrid(ctx, p, res);
     const long long n = ctx->nrows; const int F = ctx->F;
-    const long long xoff = ctx->strip.col_lo * F, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F;
-    const long long nfull = ctx->general_csr ? n : (ctx->strip.col_hi - ctx->strip.col_lo) * F;      // interface problem: whole mesh, its own numbering
-    if (!ctx->x) {
-        CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
-        CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
-        CK(dalloc(ctx, &ctx->parts, (size_t)4 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
-        CK(cudaMemsetAsync(ctx->dfull, 0, (size_t)nfull * 8, ctx->stream));
-    }
-    ctx->d = ctx->dfull + down;
     const bool multi = ctx->world > 1;
-    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
-    int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
-    long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
+    const SpmvPlan plan = make_spmv_plan(ctx);
+    const int nblk = plan.nblk, nblk_sp = plan.nblk_sp;
     double *p_dy = ctx->parts, *p_rr = ctx->parts + 2 * PCG_MAX_BLOCKS, *p_rz = ctx->parts + 3 * PCG_MAX_BLOCKS;      // d.y: block SpMV partials, then the irregular-row pass
     double *s_dy = ctx->scal, *s_rr = ctx->scal + 1, *s_rz = ctx->scal + 2;
     // what the consuming kernels read: the per-block partials (one rank) or the all-reduced scalars (several)
@@ -140,20 +203,9 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     const int c_n = multi ? 1 : nblk;
     const int pre = p->apply_preconditioner ? 1 : 0;
     const bool blockpre = p->apply_preconditioner == 2 && F >= 2 && F <= 4;      // F = 1: the block is the diagonal
-    if (blockpre && !ctx->iAb) CK(dalloc(ctx, &ctx->iAb, (size_t)n * F));
+    if (blockpre) { pb_status st = ensure_block_inverse(ctx); if (st != PB_OK) return st; }
     const long long nbr_own = n / F;
-    const int lpr = spmv_lanes(F);
-    const bool use_csr = getenv("PB_SPMV_CSR") != nullptr || F > 4 || F == 1 || (ctx->general_csr && !ctx->ifc_struct_ok);
-    // interface problem: block kernel on the block rows in interface order + a scalar pass over the rows of the cut cells' faces
-    const int nblk_irr = (!use_csr && ctx->general_csr && ctx->n_irr_rows > 0) ? (int)std::min<long long>(PCG_MAX_BLOCKS, ((long long)ctx->n_irr_rows * F + 7) / 8) : 0;   // one warp per scalar row   // scalar CSR: comparison runs, and F = 1 where a
-                                                                               // 64-byte face record per row costs more than 7 column indices
-    int nblk_sp = nblk;                                                  // grid of the SpMV = number of d.y partials
-    if (!use_csr) {
-        const int occ = F == 1 ? spmv_blk_blocks_per_sm<1>() : F == 2 ? spmv_blk_blocks_per_sm<2>() : F == 3 ? spmv_blk_blocks_per_sm<3>() : spmv_blk_blocks_per_sm<4>();
-        nblk_sp = nsm * occ; if (nblk_sp > PCG_MAX_BLOCKS) nblk_sp = PCG_MAX_BLOCKS;
-        const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < nblk_sp) nblk_sp = (int)(wantg < 1 ? 1 : wantg);
-    }
-    const int c_ndy = multi ? 1 : nblk_sp + nblk_irr;
+    const int c_ndy = multi ? 1 : plan.ndy();
     cudaStream_t sm = ctx->stream;
     auto reduce_rr_rz = [&]() -> pb_status {
         if (!multi) return PB_OK;
@@ -169,7 +221,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
         if (F == 2) PB_BJ(2); else if (F == 3) PB_BJ(3); else PB_BJ(4);
 #undef PB_BJ
     } else {
-        pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
+        pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->general_csr ? 0 : ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
         pcg_init_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
     }
     { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }
@@ -178,18 +230,7 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     // one iteration = [dir, commit] (skipped in the very first one), halo exchange, spmv, xrz (+ all-reduces)
     auto spmv_xrz = [&]() -> pb_status {
         { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
-#define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<nblk_sp, PCG_THREADS, 0, sm>>>(n, xoff, ctx->brows, ctx->brp, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg)
-        if (use_csr) {
-            switch (lpr) {
-            case 4: pcg_spmv_kernel<4><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-            case 8: pcg_spmv_kernel<8><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-            default: pcg_spmv_kernel<16><<<nblk, PCG_THREADS, 0, sm>>>(n, xoff, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, down, ctx->y, p_dy, ctx->cg); break;
-            }
-        } else {
-            switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
-        }
-#undef PB_SPMV
-        if (nblk_irr) pcg_spmv_rows_kernel<<<nblk_irr, PCG_THREADS, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rowptr, ctx->col, ctx->val, ctx->dfull, ctx->y, p_dy + nblk_sp, ctx->cg);
+        { pb_status st = launch_spmv(ctx, plan, ctx->dfull, ctx->y, p_dy); if (st != PB_OK) return st; }
         if (multi) {
             pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk_sp, p_dy, s_dy, nullptr, nullptr);
             NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
@@ -218,8 +259,8 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
         CK(cudaStreamBeginCapture(sm, cudaStreamCaptureModeThreadLocal));
         pb_status cst = PB_OK;
         for (int k = 0; k < check_every && cst == PB_OK; k++) cst = full_iteration();
-        cudaError_t ce = cudaStreamEndCapture(sm, &graph);
-        if (cst != PB_OK) return cst;
+        cudaError_t ce = cudaStreamEndCapture(sm, &graph);      // always closes the capture, also on the error path
+        if (cst != PB_OK) { if (graph) cudaGraphDestroy(graph); return cst; }
         CK(ce);
         CK(cudaGraphInstantiate(&gexec, graph, 0));
     }

@@ -43,6 +43,7 @@ extern "C" pb_status pb_obstacle_iterate(pb_ctx* ctx, const pb_cg_params* cgp, d
     else obstacle_condense_kernel<1><<<G, B, 0, ctx->stream>>>(g, nc, ctx->points, ctx->lc, ctx->rhsloc, ctx->ob_alpha, ctx->ob_beta, ctx->ob_gamma, 1.0, ctx->prm.fun, ctx->ob_inA, ctx->S, ctx->g, d_act);
     CK(cudaGetLastError());
     { pb_status st = scatter_system(ctx); if (st != PB_OK) return st; }
+    ctx->asm_gen++;      // new system values: cached preconditioner data is stale
     pb_cg_result res{};
     { pb_status st = pb_pcg(ctx, cgp, &res); if (st != PB_OK) return st; }
     if (fd == 0) obstacle_update_kernel<0><<<G, B, 0, ctx->stream>>>(g, nc, ctx->points, ctx->lc, ctx->rhsloc, ctx->x, ctx->ob_inA, ctx->ob_gamma, ctx->prm.fun, ctx->ob_alpha, ctx->ob_beta, parts);
