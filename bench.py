@@ -13,6 +13,7 @@ host buffers: pinned host points -> device, assemble, condensed rhs -> pinned ho
 import argparse
 import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
@@ -129,10 +130,29 @@ def host_threads(orc):
         return max(1, os.cpu_count() or 1)
 
 
-def cut_record(args, rank, world, dev, dist, torch, pb, PB):
-    """Secondary record (not the headline): BASELINE's target, cutHHO fictitious-domain Poisson k=2, circle level set, on
-    cut_N x cut_N quads sharded by cell rows over the ranks (fixed total size).  Preprocessing on the device, assembly
-    (K1 Dunavant-fan uncut cells + K2 cut cells + K3), a fixed number of PCG iterations for the bandwidth figure."""
+# flop model of one cell of the fictitious-domain driver at k=2 (SURVEY 8d formulas): uncut cells = the naive-
+# stabilisation total (47.8 k) with the 16-point tensor rule replaced by the 4 x 13-point Dunavant fan of degree 2 rd = 6
+# (stiffness 4 R^2, load 2 C and 3 flop per basis entry for every extra point); cut cells = Qc = ntri x 13 points over the
+# triangulated negative part (ntri = 3..5 + 2^r segments), Qi = 2^r (rd + 1) interface points x 6 R^2 for the Nitsche terms, m = R
+def flop_dunavant_naive(k):
+    R = (k + 2) * (k + 3) // 2; C = R
+    naive = {0: 1.7e3, 1: 12.3e3, 2: 47.8e3}[k]
+    q_tensor = (k + 2) ** 2; q_fan = 4 * {0: 4, 1: 7, 2: 13}[k]          # degree 2 rd = 2, 4, 6 -> Dunavant rule rd*2+1
+    return naive + (q_fan - q_tensor) * (4 * R * R + 2 * C + 9 * R)
+
+
+def flop_cut_cell(k, refine_steps=4):
+    R = (k + 2) * (k + 3) // 2; C = R; F = k + 1; n = C + 4 * F
+    qc = (4 + 2 ** refine_steps) * {0: 4, 1: 7, 2: 13}[k]; qi = 2 ** refine_steps * (k + 2)
+    return qc * (4 * R * R + 2 * C + 9 * R) + qi * 6 * R * R + R ** 3 / 3 + 2 * R * R * n + 2 * n * n * R + flop_dunavant_naive(k) * 0.45
+
+
+def cut_record(args, rank, world, dev, dist, torch, pb, PB, fp64_peak):
+    """BASELINE's target: cutHHO fictitious-domain Poisson k=2, circle level set r=0.35 (cuthho_square.cpp:2030), on
+    cut_N x cut_N quads sharded by cell rows over the ranks (fixed total size): preprocessing on the device, assembly
+    (K1 Dunavant-fan uncut cells + K2 cut cells + K3), the solve to the driver's tolerance (cg_params default 1e-9,
+    cuthho_square.cpp:1736-1743) with the multigrid preconditioner, the driver's H1 error (:1031-1064) summed over the
+    ranks, and a fixed number of iterations of the reference's Jacobi-PCG for the bandwidth figure."""
     from proton_b200.dist import make_rank_context
     Nc, k = args.cut_N, 2
     hdi = pb.hho_degree_info(k + 1, k)
@@ -142,34 +162,82 @@ def cut_record(args, rank, world, dev, dist, torch, pb, PB):
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize(dev)
+
+    def allmax(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        tt = torch.tensor(vals, dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); return [float(v) for v in tt.tolist()]
+
+    def allsum(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        tt = torch.tensor(vals, dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt); return [float(v) for v in tt.tolist()]
     sync_all(); t0 = time.perf_counter()
-    ctx.cut_levelset(0, 1.0 / 3.0, 0.5, 0.5)
+    ctx.cut_levelset(0, 0.35, 0.5, 0.5)
     ctx.cut_preprocess(4)
     sync_all(); prep_ms = (time.perf_counter() - t0) * 1e3
     for _ in range(2):
         ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
     sync_all()
-    ms = []
+    ms, loc = [], []
     for _ in range(3):
         ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
-        t = ctx.timings(); ms.append(t["ms_local"] + t["ms_scatter"])
-    asm_ms = sum(ms) / len(ms)
+        t = ctx.timings(); ms.append(t["ms_local"] + t["ms_scatter"]); loc.append(t["ms_local"])
+    asm_ms, loc_ms = sum(ms) / len(ms), sum(loc) / len(loc)
+    # the solve, to the driver's tolerance, multigrid-preconditioned (setup included in the time)
+    sync_all(); t0 = time.perf_counter()
+    r_mg = ctx.conjugated_gradient(pb.cg_params(1e-9, 1e8, 20000, 3))
+    sync_all(); solve_ms = (time.perf_counter() - t0) * 1e3
+    nlev, lmax, _ = ctx.mg_info()
+    h1 = math.sqrt(allsum([ctx.error_norms()[0]])[0])
+    # a tighter solve: how far the discretisation error is from the solver tolerance
+    r_mg2 = ctx.conjugated_gradient(pb.cg_params(1e-12, 1e8, 20000, 3))
+    h1_tight = math.sqrt(allsum([ctx.error_norms()[0]])[0])
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 20, True))
     sync_all()
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 100, True))
     it_ms = ctx.timings()["ms_pcg"] / 101.0
-    vals = [asm_ms, it_ms, prep_ms]
-    nnz, rows, ncut = ctx.nnz, ctx.n_rows, ctx.cut_counts()[0]
-    if dist is not None:
-        tt = torch.tensor(vals, dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); vals = [float(v) for v in tt.tolist()]
-        tt = torch.tensor([nnz, rows], dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt); nnz, rows = int(tt[0]), int(tt[1])
+    asm_ms, it_ms, prep_ms, loc_ms, solve_ms = allmax([asm_ms, it_ms, prep_ms, loc_ms, solve_ms])
+    ncut = ctx.cut_counts()[0]                       # every rank preprocesses the whole level set
+    nnz, rows, cells_k1 = [int(v) for v in allsum([ctx.nnz, ctx.n_rows, ctx.ncells_local])]
     ctx.close()
     hbm, _ = peaks()
     iter_bytes = (8.0 * nnz + 64.0 * rows / hdi.fbs + 16.0 * rows + 11 * 8.0 * rows) / world
-    return {"workload": f"cutHHO fictitious-domain Poisson k=2, circle level set r=1/3, {Nc}x{Nc} quads sharded over {world} GPU(s) by cell rows (BASELINE target; "
+    flops = (cells_k1 - ncut) * flop_dunavant_naive(k) + ncut * flop_cut_cell(k)       # all ranks, ghost rows included (they are computed)
+    tf = flops / world / (loc_ms * 1e-3) / 1e12
+    return {"workload": f"cutHHO fictitious-domain Poisson k=2, circle level set r=0.35, {Nc}x{Nc} quads sharded over {world} GPU(s) by cell rows (BASELINE target; "
                         "k=3 of config 4 has no valid reference answer, SURVEY F4)",
-            "preprocess_ms": vals[2], "assemble_ms": vals[0], "cells_per_s": Nc * Nc / (vals[0] * 1e-3), "cut_cells": ncut,
-            "pcg_ms_per_iter": vals[1], "pcg_hbm_frac": iter_bytes / (vals[1] * 1e-3) / 1e9 / hbm, "unknowns": rows, "nnz": nnz}
+            "preprocess_ms": prep_ms, "assemble_ms": asm_ms, "local_ms": loc_ms, "cells_per_s": Nc * Nc / (asm_ms * 1e-3), "cut_cells": ncut,
+            "unknowns": rows, "nnz": nnz,
+            "solve": {"preconditioner": "multigrid (apply_preconditioner=3; not reference behaviour)", "tol": 1e-9, "iterations": r_mg["iterations"],
+                      "exit_reason": r_mg["exit_reason"], "relative_residual": r_mg["relative_residual"], "solve_ms": solve_ms, "mg_levels": nlev, "smoother_lmax": lmax,
+                      "h1_error": h1, "tight": {"tol": 1e-12, "iterations": r_mg2["iterations"], "exit_reason": r_mg2["exit_reason"], "h1_error": h1_tight,
+                                                "h1_rel_diff": abs(h1 - h1_tight) / h1_tight}},
+            "pcg_ms_per_iter": it_ms, "pcg_hbm_frac": iter_bytes / (it_ms * 1e-3) / 1e9 / hbm, "pcg_note": "the reference's Jacobi-PCG, 100 fixed iterations",
+            "roofline": {"bound": "fp64", "kernel": "local_uncut_kernel<3,2,Dunavant,naive> + local_cut_kernel<3,2> (K1 + K2)", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s per GPU",
+                         "frac": tf / fp64_peak, "flop_per_uncut_cell": flop_dunavant_naive(k), "flop_per_cut_cell": flop_cut_cell(k), "ms_per_launch": loc_ms,
+                         "flop_model": "reference-algorithm flops (SURVEY 8d; BASELINE.md 4), not executed flops"}}
+
+
+def obstacle_record(args, dev, pb, PB):
+    """BASELINE config 5 (single GPU): HHO obstacle problem, face degree 1, ob_N x ob_N quads on [-1,1]^2, the driver's active-set
+    loop (obstacle.cpp:119-198, capped at 50 outer iterations like the reference)."""
+    N = args.ob_N
+    ctx = pb.Context(dev)
+    ctx.mesh(pb.mesh_init_params(N, N, -1.0, 1.0, -1.0, 1.0))
+    out = {"workload": f"HHO(0,1) obstacle problem on {N}x{N} quads (BASELINE config 5), primal-dual active set, 50-iteration cap of obstacle.cpp:119"}
+    for name, pre in (("multigrid", 3), ("jacobi", 1)):
+        if pre == 1 and args.ob_skip_jacobi:
+            continue
+        t0 = time.perf_counter()
+        try:
+            err, outer, log = ctx.obstacle_solve(1, cgp=pb.cg_params(1e-13, 1e300, 1000000, pre))
+        except Exception as e:          # recorded, not fatal for the headline line
+            out[name] = {"failed": str(e)[:200]}; continue
+        out[name] = {"outer_iterations": outer, "stopped_on_cap": outer >= 50, "pcg_iterations": int(sum(l[2] for l in log)), "seconds": time.perf_counter() - t0,
+                     "error": err, "active_cells": int(log[-1][1]), "unknowns": ctx.n_rows}
+    ctx.close()
+    return out
 
 
 def interface_record(args, dev, pb, PB):
@@ -288,13 +356,6 @@ def run_ours(args, rank, world, local_rank):
     # face, x read + y write per row.  (The scalar-CSR product of SURVEY §8d would move 12*nnz + 20*n.)
     spmv_bytes = (8.0 * nnz + 64.0 * n_rows / hdi.fbs + 16.0 * n_rows) if hdi.fbs > 1 else (12.0 * nnz + 20.0 * n_rows)
     iter_bytes = spmv_bytes + 11 * 8.0 * n_rows                 # + vector passes of the dir / xrz kernels
-    r_tol = t_tol = None
-    if world == 1 and not args.no_cg_tol:
-        ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))          # warm-up + the reference's own problem
-        r_tol = ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))
-        t_tol = ctx.timings()["ms_pcg"]
-        r_bj = ctx.conjugated_gradient(pb.cg_params(1e-12, 1e8, 3 * n_rows, 2))             # extension: fbs x fbs block-Jacobi
-        t_bj = ctx.timings()["ms_pcg"]
     fixed = 200
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 40, True))
     sync_all()
@@ -310,10 +371,26 @@ def run_ours(args, rank, world, local_rank):
           "halo_doubles_per_neighbour": (2 * Nx - 1) * hdi.fbs, "allreduces_per_iter": 2 if world > 1 else 0,
           "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s per GPU", "frac": gbs / hbm, "peak_source": hbm_src,
                        "traffic": (ncu_traffic("pcg_spmv_blk_kernel", N, k) or {}).get("bytes"), "traffic_note": "SpMV kernel alone (algorithmic %.3g B), single-GPU capture" % spmv_bytes}}
-    if r_tol is not None:
-        cg.update({"tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": t_tol,
-                   "block_jacobi": {"iterations": r_bj["iterations"], "exit_reason": r_bj["exit_reason"], "solve_ms": t_bj,
-                                    "note": "apply_preconditioner=2, not reference behaviour; the headline solve is the reference's diagonal preconditioner"}})
+    if world == 1 and not args.no_cg_tol:
+        r_tol = ctx.conjugated_gradient(pb.cg_params(1e-12, 100.0, 3 * n_rows, True))      # the reference's solver on the reference's own problem
+        cg.update({"tol": 1e-12, "iterations": r_tol["iterations"], "exit_reason": r_tol["exit_reason"], "solve_ms": ctx.timings()["ms_pcg"],
+                   "note": "the reference's diagonal preconditioner (solver_cg.hpp:78-81); convergence_test.cpp:238-241 settings"})
+    # the same solve with the multigrid preconditioner (apply_preconditioner=3, not reference behaviour), all ranks together
+    sync_all(); t0 = time.perf_counter()
+    r_mg = ctx.conjugated_gradient(pb.cg_params(1e-12, 1e8, 1000, 3))
+    sync_all(); t_mg_first = (time.perf_counter() - t0) * 1e3
+    nlev, lmax, _ = ctx.mg_info()
+    sync_all(); t0 = time.perf_counter()
+    r_mg = ctx.conjugated_gradient(pb.cg_params(1e-12, 1e8, 1000, 3))
+    sync_all(); t_mg = (time.perf_counter() - t0) * 1e3
+    e_mg = ctx.error_norms()
+    if dist is not None:
+        tt = torch.tensor([t_mg_first, t_mg], dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); t_mg_first, t_mg = float(tt[0]), float(tt[1])
+        tt = torch.tensor(list(e_mg), dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(tt); e_mg = tt.tolist()
+    cg["multigrid"] = {"tol": 1e-12, "iterations": r_mg["iterations"], "exit_reason": r_mg["exit_reason"], "relative_residual": r_mg["relative_residual"],
+                       "solve_ms_with_setup": t_mg_first, "solve_ms": t_mg, "levels": nlev, "smoother_lmax": lmax,
+                       "l2_error": math.sqrt(abs(e_mg[0])), "energy_error": math.sqrt(abs(e_mg[2])),
+                       "note": "apply_preconditioner=3: Chebyshev/block-Jacobi smoothing on the face system + Galerkin vertex levels; wall clock between barriers, max over ranks"}
 
     # ---------------- reduce over ranks (max time), print on rank 0
     if dist is not None:
@@ -347,7 +424,9 @@ def run_ours(args, rank, world, local_rank):
            "gpu_launches": 2 * args.steps, "cg": cg}
     ctx.close()
     if not args.no_cut:
-        out["target_cut"] = cut_record(args, rank, world, dev, dist, torch, pb, PB)
+        out["target_cut"] = cut_record(args, rank, world, dev, dist, torch, pb, PB, fp64_peak)
+    if world == 1 and not args.no_obstacle:
+        out["obstacle"] = obstacle_record(args, dev, pb, PB)
     if world == 1 and not args.no_interface:
         out["interface"] = interface_record(args, dev, pb, PB)
     if rank == 0:
@@ -382,6 +461,9 @@ def main():
     ap.add_argument("--cut-N", dest="cut_N", type=int, default=4096)
     ap.add_argument("--no-interface", action="store_true", help="skip the secondary record of the two-material interface problem")
     ap.add_argument("--ifc-N", dest="ifc_N", type=int, default=2048)
+    ap.add_argument("--no-obstacle", action="store_true", help="skip the secondary record of the obstacle problem (config 5)")
+    ap.add_argument("--ob-N", dest="ob_N", type=int, default=1024)
+    ap.add_argument("--ob-skip-jacobi", action="store_true", help="obstacle record: only the multigrid-preconditioned loop")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))

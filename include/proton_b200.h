@@ -46,7 +46,9 @@ typedef struct {
     int fun;                           /* pb_fun_kind: source term, Dirichlet / Nitsche data, exact solution */
     int rhs_degree_increase;           /* `di` of make_rhs (utils.hpp:153-174); obstacle.cpp:102 uses 1 */
     double eta;                        /* Nitsche penalty, cell_eta() = 5 (cuthho_square.cpp:301-306) */
-    int keep_local;                    /* 1: also keep oper / (data+stab) / rhs per cell for pb_get_local */
+    int keep_local;                    /* 1: also keep oper / (data+stab) / rhs per cell for pb_get_local; 2: additionally gr.second
+                                        * (`data`) apart from the stabilisation (selector 7) — the per-cell views of the C++ shim;
+                                        * this routes the uncut cells through the literal, untuned kernel (pb_generic.cuh) */
 } pb_assembly_params;
 
 /* cg_params (solver_cg.hpp:44-61).  apply_preconditioner: 0 = none, 1 = the reference's diagonal preconditioner
@@ -118,7 +120,8 @@ pb_status pb_system_sizes(pb_ctx* ctx, long long* n_rows, long long* nnz, long l
 pb_status pb_get_csr(pb_ctx* ctx, long long* rowptr, int* col, double* val, double* rhs);
 /* per-cell dense results, column-major like Eigen, for cells [cell_begin, cell_begin+count):
  * what = 0: lc = gr.second + stab (n x n); 1: oper = gr.first ((rbs-1) x n, or rbs x n rows padded layout, see
- * DESIGN.md); 2: cell rhs (cbs); 3: condensed block S (4fbs x 4fbs); 4: condensed rhs g (4fbs). 0-2 need keep_local. */
+ * DESIGN.md); 2: cell rhs (cbs); 3: condensed block S (4fbs x 4fbs); 4: condensed rhs g (4fbs); 5: K_TT^-1 K_TF (cbs x 4fbs);
+ * 6: K_TT^-1 f_T (cbs); 7: data = gr.second (n x n).  0-2 need keep_local, 7 needs keep_local = 2. */
 pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, long long count, double* out);
 
 /* ---- stage 3: conjugated_gradient(A, b, x, cg_params) (solver_cg.hpp:63-144) on the condensed system ---- */
@@ -128,6 +131,10 @@ pb_status pb_set_face_solution(pb_ctx* ctx, const double* x);
 /* back-substitution: the reference's FULL solution vector (cell dofs c*cbs+i, then face dofs
  * cbs*ncells + compress[f]*fbs + a), hho.hpp:362-379 */
 pb_status pb_recover(pb_ctx* ctx, double* full_solution);
+/* assembler.take_local_data(msh, cl, sol, bf) (hho.hpp:408-449) for the owned cells [cell_begin, cell_begin + count) (0 = the first
+ * owned cell): n_local = cbs + 4 fbs values per cell, the cell dofs, then the dofs of faces(msh, cl) with the Dirichlet faces
+ * replaced by the projection of the datum */
+pb_status pb_get_local_solution(pb_ctx* ctx, long long cell_begin, long long count, double* local_dofs);
 /* error norms of the drivers: out[0..2] = sums of squares of convergence_test.cpp:254-306 (L2, mass-norm, energy)
  * for PB_PROBLEM_HHO; out[0] = H1 error^2 of cuthho_square.cpp:1031-1050 for PB_PROBLEM_FICTDOM.  A strip context
  * returns the sums over its owned cells (add them over the ranks). */

@@ -48,7 +48,7 @@ struct pb_ctx {
     bool assembled = false;
     pb_assembly_params prm{};
     int CD = 0, FD = 0, C = 0, F = 0, R = 0, N = 0, NF = 0;
-    double *S = nullptr, *g = nullptr, *recA = nullptr, *recb = nullptr, *lc = nullptr, *oper = nullptr, *rhsloc = nullptr;
+    double *S = nullptr, *g = nullptr, *recA = nullptr, *recb = nullptr, *lc = nullptr, *oper = nullptr, *rhsloc = nullptr, *data = nullptr;
     long long nrows_blk = 0, nrows = 0, nnz = 0;
     BlockRow* brows = nullptr; long long* brp = nullptr;
     long long* rowptr = nullptr; int* col = nullptr; double *val = nullptr, *rhs = nullptr;
@@ -170,7 +170,7 @@ static void free_solver(pb_ctx* c) {
     mg_free(c);
 }
 static void free_system(pb_ctx* c) {
-    dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc);
+    dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc); dfree(&c->data);
     dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); dfree(&c->irr_rows); c->n_irr_rows = 0; dfree(&c->irr_faces); c->n_irr_faces = 0; c->ifc_struct_ok = false;
     dfree(&c->ifc_k0); dfree(&c->ifc_k1); dfree(&c->ifc_v0); dfree(&c->ifc_v1); dfree(&c->ifc_dnum); if (c->ifc_tmp) { cudaFree(c->ifc_tmp); c->ifc_tmp = nullptr; } c->ifc_T = 0; c->ifc_ncut_alloc = 0; c->general_csr = false;
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
@@ -400,6 +400,9 @@ static pb_status launch_generic(pb_ctx* ctx, const LocalArgs& A, int cd, int fd,
         if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "local_generic_kernel launch failed: %s", cudaGetErrorString(e)); \
         return PB_OK; }
     PB_GEN(0, 0) PB_GEN(0, 1) PB_GEN(1, 1) PB_GEN(2, 2) PB_GEN(1, 2)
+#ifndef PB_FAST_BUILD
+    PB_GEN(1, 0) PB_GEN(2, 1) PB_GEN(3, 2) PB_GEN(4, 3)      // HHO(k+1,k) through the literal kernel: keep_local = 2 (per-cell views of the C++ shim)
+#endif
 #undef PB_GEN
     *found = false; return PB_OK;
 }
@@ -444,7 +447,7 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");
     int sk = p->stab_kind == PB_STAB_FANCY ? 1 : 0;
     const int rqd = 2 * (cd + p->rhs_degree_increase);
-    bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc) || ctx->general_csr != ifc;
+    bool relayout = !ctx->S || ctx->CD != cd || ctx->FD != fd || (p->keep_local && !ctx->lc) || (p->keep_local == 2 && !ctx->data) || ctx->general_csr != ifc;
     ctx->prm = *p; ctx->CD = cd; ctx->FD = fd;
     ctx->C = cell_basis_size(cd); ctx->F = fd + 1; ctx->R = cell_basis_size(fd + 1); ctx->NF = 4 * ctx->F; ctx->N = ctx->C + ctx->NF;
     const long long nc = ctx->ncells_local;
@@ -455,6 +458,7 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
         if (p->keep_local) {
             CK(dalloc(ctx, &ctx->lc, (size_t)nc * ctx->N * ctx->N)); CK(dalloc(ctx, &ctx->oper, (size_t)nc * ctx->N * ctx->R));
             CK(dalloc(ctx, &ctx->rhsloc, (size_t)nc * ctx->C));
+            if (p->keep_local == 2) CK(dalloc(ctx, &ctx->data, (size_t)nc * ctx->N * ctx->N));
         }
         if (!ifc) { pb_status st = build_structure(ctx); if (st != PB_OK) return st; }
         ctx->general_csr = ifc;
@@ -465,6 +469,8 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     A.ncells = nc; A.fun = p->fun; A.problem = p->problem; A.eta = p->eta;
     A.S = ctx->S; A.g = ctx->g; A.recA = ctx->recA; A.recb = ctx->recb;
     A.lc = p->keep_local ? ctx->lc : nullptr; A.oper = p->keep_local ? ctx->oper : nullptr; A.rhs = p->keep_local ? ctx->rhsloc : nullptr;
+    A.data = p->keep_local == 2 ? ctx->data : nullptr;
+    NEED(!(ifc && p->keep_local == 2), PB_ERR_UNSUPPORTED, "pb_assemble: keep_local = 2 (gr.second apart from the stabilisation) is built for the plain and fictitious-domain problems");
     if (host_points) {
         if (!ctx->s_in) { CK(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming)); }
         if (ctx->pipe_in_flight) CK(cudaStreamWaitEvent(ctx->s_in, ctx->ev[1], 0));      // previous K1 has read the vertices
@@ -476,7 +482,8 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     }
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     bool found = false;
-    CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
+    // keep_local = 2 asks for gr.second apart from the stabilisation: only the literal kernels hold the two separately
+    if (p->keep_local != 2) CK(dispatch_local(ctx, A, cd, fd, ctx->quad_kind, sk, rqd, &found));
     if (!found) { pb_status st = launch_generic(ctx, A, cd, fd, ctx->quad_kind, sk, p->rhs_degree_increase, &found); if (st != PB_OK) return st; }
     if (!found) return fail(ctx, PB_ERR_UNSUPPORTED, "pb_assemble: no kernel instance for HHO(%d,%d) quad_kind=%d stab=%d load degree %d", cd, fd, ctx->quad_kind, p->stab_kind, rqd);
     if (p->problem == PB_PROBLEM_FICTDOM && ctx->ncut > 0) {
@@ -562,9 +569,10 @@ extern "C" pb_status pb_get_local(pb_ctx* ctx, int what, long long cell_begin, l
     case 4: src = ctx->g; per = ctx->NF; break;
     case 5: src = ctx->recA; per = (long long)ctx->NF * ctx->C; break;
     case 6: src = ctx->recb; per = ctx->C; break;
+    case 7: src = ctx->data; per = (long long)ctx->N * ctx->N; break;
     default: return fail(ctx, PB_ERR_INVALID, "pb_get_local: unknown selector %d", what);
     }
-    NEED(src != nullptr, PB_ERR_STATE, "pb_get_local: assemble with keep_local=1 to read lc/oper/rhs");
+    NEED(src != nullptr, PB_ERR_STATE, "pb_get_local: assemble with keep_local = 1 to read lc / oper / rhs, keep_local = 2 to read gr.second (selector 7)");
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemcpy(out, src + cell_begin * per, (size_t)(count * per) * 8, cudaMemcpyDeviceToHost));
     return PB_OK;
@@ -591,7 +599,7 @@ extern "C" pb_status pb_set_face_solution(pb_ctx* ctx, const double* x) {
 template <int FD>
 __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, long long row_first_owned, int C, int fun, const double2* __restrict__ points,
                                const double* __restrict__ recA, const double* __restrict__ recb, const double* __restrict__ xf, long long xoff,
-                               double* __restrict__ ucell) {
+                               double* __restrict__ ucell, double* __restrict__ ulocal) {
     constexpr int F = FD + 1, NF = 4 * F, QF = FD + 1;
     for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x) {
         long long ci = c % g.Nx, cj = cell_row0 + c / g.Nx;
@@ -642,7 +650,10 @@ __global__ void recover_kernel(Grid g, long long cell_row0, long long ncells, lo
 #pragma unroll
             for (int i = 0; i < NF; i++) v -= recA[(c * NF + i) * C + k] * uF[i];
             ucell[gc * C + k] = v;
+            if (ulocal) ulocal[(gc - row_first_owned * g.Nx) * (C + NF) + k] = v;
         }
+        if (ulocal)       // take_local_data (hho.hpp:408-449): cell dofs, then the face dofs with the Dirichlet faces projected
+            for (int i = 0; i < NF; i++) ulocal[(gc - row_first_owned * g.Nx) * (C + NF) + C + i] = uF[i];
     }
 }
 

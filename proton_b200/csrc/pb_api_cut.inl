@@ -137,7 +137,7 @@ static pb_status launch_cut(pb_ctx* ctx, const LocalArgs& L, int cd, int fd) {
     A.cut_cells = ctx->cut_cells; A.iface = ctx->iface; A.ncut = ctx->ncut; A.NI = ctx->NI;
     A.cell_begin = ctx->strip.cell_row0 * ctx->grid.Nx; A.cell_end = A.cell_begin + ctx->ncells_local;
     A.fun = L.fun; A.eta = L.eta;
-    A.S = L.S; A.g = L.g; A.recA = L.recA; A.recb = L.recb; A.lc = L.lc; A.oper = L.oper; A.rhs = L.rhs;
+    A.S = L.S; A.g = L.g; A.recA = L.recA; A.recb = L.recb; A.lc = L.lc; A.oper = L.oper; A.rhs = L.rhs; A.data = L.data;
     cudaError_t e;
     if (cd == 1 && fd == 0) e = launch_cut_t<1, 0>(ctx, A);
     else if (cd == 2 && fd == 1) e = launch_cut_t<2, 1>(ctx, A);

@@ -302,7 +302,7 @@ extern "C" pb_status pb_pcg_get_history(pb_ctx* ctx, double* out, long long capa
 }
 
 // back-substitution (K6) for the owned cell rows; xfull = face solution for the columns [col_lo, col_hi)
-static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** keep_uc = nullptr, double** keep_xfull = nullptr) {
+static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** keep_uc = nullptr, double** keep_xfull = nullptr, double* ulocal_dev = nullptr) {
     const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;
     const long long n = ctx->nrows, down = (ctx->strip.cf_begin - ctx->strip.col_lo) * F, nfull = (ctx->strip.col_hi - ctx->strip.col_lo) * F;
     const long long owned_cells = (g.row_end - g.row_begin) * g.Nx;
@@ -313,7 +313,7 @@ static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** kee
     { pb_status st = halo_exchange(ctx, xfull); if (st != PB_OK) return st; }
     double* uc_shift = uc - g.row_begin * g.Nx * C;          // the kernel indexes cell dofs by GLOBAL cell id
 #define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, ctx->strip.cell_row0, ctx->ncells_local, g.row_begin, C, ctx->prm.fun, \
-        ctx->points, ctx->recA, ctx->recb, xfull, ctx->strip.col_lo * F, uc_shift)
+        ctx->points, ctx->recA, ctx->recb, xfull, ctx->strip.col_lo * F, uc_shift, ulocal_dev)
     switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; case 2: PB_REC(2); break; case 3: PB_REC(3); break;
     default: cudaFree(uc); cudaFree(xfull); return fail(ctx, PB_ERR_UNSUPPORTED, "pb_recover: face degree %d", ctx->FD); }
 #undef PB_REC
@@ -333,6 +333,21 @@ extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* fa
     pb_status st = recover_owned(ctx, cell_dofs); if (st != PB_OK) return st;
     if (face_dofs) CK(cudaMemcpy(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
     return PB_OK;
+}
+
+// take_local_data (hho.hpp:408-449) of every owned cell: cbs cell dofs, then 4 fbs face dofs, Dirichlet faces projected
+extern "C" pb_status pb_get_local_solution(pb_ctx* ctx, long long cell_begin, long long count, double* out) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->assembled && ctx->x && out && ctx->solver_n == ctx->nrows, PB_ERR_STATE, "pb_get_local_solution: no face solution");
+    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_get_local_solution: plain and fictitious-domain problems");
+    const long long owned = (ctx->grid.row_end - ctx->grid.row_begin) * ctx->grid.Nx;
+    NEED(cell_begin >= 0 && count >= 0 && cell_begin + count <= owned, PB_ERR_INVALID, "pb_get_local_solution: cell range out of bounds (owned cells, 0-based)");
+    CK(cudaSetDevice(ctx->device));
+    double* ul = nullptr; CK(cudaMalloc((void**)&ul, (size_t)owned * ctx->N * 8));
+    pb_status st = recover_owned(ctx, nullptr, nullptr, nullptr, ul);
+    if (st == PB_OK) { cudaError_t e = cudaMemcpy(out, ul + cell_begin * ctx->N, (size_t)count * ctx->N * 8, cudaMemcpyDeviceToHost); if (e != cudaSuccess) st = fail(ctx, PB_ERR_CUDA, "pb_get_local_solution: %s", cudaGetErrorString(e)); }
+    cudaFree(ul);
+    return st;
 }
 
 // the reference's FULL solution vector (cell dofs c*cbs+i, then face dofs cbs*ncells + compress[f]*fbs + a)

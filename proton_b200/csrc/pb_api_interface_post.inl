@@ -239,7 +239,7 @@ static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** 
     CK(cudaMalloc((void**)&xreg, (size_t)nreg * 8)); CK(cudaMalloc((void**)&uc, (size_t)nc * C * 8));
     CK(cudaMalloc((void**)&ucut, (size_t)(ctx->ncut > 0 ? ctx->ncut : 1) * 2 * C * 8));
     ifc_gather_regular_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, F, ctx->ftab, ctx->x, xreg);
-#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, 0, nc, 0, C, ctx->prm.fun, ctx->points, ctx->recA, ctx->recb, xreg, 0, uc)
+#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, 0, nc, 0, C, ctx->prm.fun, ctx->points, ctx->recA, ctx->recb, xreg, 0, uc, nullptr)
     switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; default: PB_REC(2); break; }
 #undef PB_REC
     if (ctx->ncut > 0)

@@ -26,6 +26,7 @@ struct CutArgs {
     long long cell_begin, cell_end; // global cell range stored by this context (local index = global - cell_begin)
     int fun; double eta;
     double *S, *g, *recA, *recb, *lc, *oper, *rhs;     // same layout as LocalArgs
+    double* data;                   // gr.second alone, or nullptr
 };
 
 constexpr int CUT_MAX_TP = 4 + 65 + 1;      // polygon of the where-part: <= 3 vertices + interface polyline (refine <= 6)
@@ -304,6 +305,7 @@ __global__ void __launch_bounds__(32) local_cut_kernel(CutArgs A) {
             double acc = 0.0;
             for (int r = 0; r < R; r++) acc += s.G[r + i * R] * s.X[r + j * R];
             s.LC[idx] = acc;
+            if (A.data) A.data[lcell * (long long)(N * N) + idx] = acc;
         }
         __syncwarp();
         // ---- make_hho_cut_stabilization (cuthho_square.cpp:566-621): naive stabilisation on the where-part of each

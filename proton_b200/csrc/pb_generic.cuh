@@ -37,6 +37,9 @@ __global__ void __launch_bounds__(32) local_generic_kernel(LocalArgs A, int rhs_
     const Grid& g = A.grid;
 
     for (long long cell = blockIdx.x; cell < A.ncells; cell += gridDim.x) {
+        int loc = PB_IN_NEGATIVE_SIDE;
+        if (A.cell_loc) { loc = A.cell_loc[cell]; if (loc == PB_ON_INTERFACE) continue; }      // cut cells: K2 (uniform per warp)
+        const bool has_load = !(A.problem == PB_PROBLEM_FICTDOM && loc != PB_IN_NEGATIVE_SIDE);   // cuthho_square.cpp:660-665
         const long long ci = cell % g.Nx, cj = g.row_begin + cell / g.Nx, p0 = grid_point(g, ci, cj);
         const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
         CellGeom geo;
@@ -104,7 +107,7 @@ __global__ void __launch_bounds__(32) local_generic_kernel(LocalArgs A, int rhs_
                     }
                     double phi[R], dx[R], dy[R];
                     eval_cell_basis<RD>((x - geo.barx) * ih, (y - geo.bary) * ih, ih, phi, dx, dy);
-                    const double wf = w * fun_rhs(A.fun, x, y);
+                    const double wf = has_load ? w * fun_rhs(A.fun, x, y) : 0.0;
 #pragma unroll
                     for (int c = 0; c < C; c++) T[c] = wf * phi[c];
                 }
@@ -158,6 +161,7 @@ __global__ void __launch_bounds__(32) local_generic_kernel(LocalArgs A, int rhs_
             s.LC[idx] = acc;
         }
         __syncwarp();
+        if (A.data) for (int idx = lane; idx < N * N; idx += 32) A.data[cell * (long long)(N * N) + idx] = s.LC[idx];      // gr.second before the stabilisation
         // ---- stabilisation
         const double hdiam = geo.h, harea = geo.area;
         if (SK == 1) {

@@ -11,6 +11,7 @@
 // views into the batch (assembler::local_contrib).  Errors are exceptions, like the reference (std::logic_error /
 // std::invalid_argument); there is no CPU fallback: without a CUDA device construction throws.
 #pragma once
+#include <array>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -96,14 +97,29 @@ public:
     }
 };
 
-// level sets of apps/cuthho/cuthho_square.cpp:56-124: host-evaluable like the reference's functors; the device uses the
-// same formulas (pb_cut_levelset)
+// point<T,2> (src/core/core_bits/point.hpp): what the drivers' functors receive
+template <typename T, size_t DIM> struct point;
+template <typename T> struct point<T, 2> {
+    T c[2];
+    point() { c[0] = c[1] = T(0); }
+    point(T x, T y) { c[0] = x; c[1] = y; }
+    T x() const { return c[0]; } T y() const { return c[1]; }
+    T& x() { return c[0]; } T& y() { return c[1]; }
+};
+
+// level sets of apps/cuthho/cuthho_square.cpp:56-124: host-evaluable like the reference's functors (operator(), gradient,
+// normal on a point); the device uses the same formulas (pb_cut_levelset)
 template <typename T>
 struct circle_level_set {
     T radius, alpha, beta, cut_y = 0;
     circle_level_set(T r, T a, T b) : radius(r), alpha(a), beta(b) {}
     int kind() const { return 0; }
     T operator()(T x, T y) const { return (x - alpha) * (x - alpha) + (y - beta) * (y - beta) - radius * radius; }
+    T operator()(const point<T, 2>& pt) const { return (*this)(pt.x(), pt.y()); }                      // :66-72
+    std::array<T, 2> gradient(const point<T, 2>& pt) const { return {{2 * pt.x() - 2 * alpha, 2 * pt.y() - 2 * beta}}; }      // :74-81
+    std::array<T, 2> normal(const point<T, 2>& pt) const {                                             // :83-90
+        auto g = gradient(pt); const T n = std::sqrt(g[0] * g[0] + g[1] * g[1]); return {{g[0] / n, g[1] / n}};
+    }
 };
 template <typename T>
 struct line_level_set {
@@ -111,6 +127,9 @@ struct line_level_set {
     explicit line_level_set(T cy) : cut_y(cy) {}
     int kind() const { return 1; }
     T operator()(T, T y) const { return y - cut_y; }
+    T operator()(const point<T, 2>& pt) const { return pt.y() - cut_y; }                               // :102-108
+    std::array<T, 2> gradient(const point<T, 2>&) const { return {{T(0), T(1)}}; }                     // :110-117
+    std::array<T, 2> normal(const point<T, 2>& pt) const { return gradient(pt); }
 };
 
 // CSR view of assembler.LHS (the condensed face system; the reference's full system has no counterpart here)

@@ -39,6 +39,14 @@ def main():
             print(f"N={Nx}x{Ny} k={k} world={world}: iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, rel diff {err:.2e}", flush=True)
             ok = ok and err < 1e-9 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2
             ref.close()
+        # multigrid-preconditioned CG (apply_preconditioner = 3) on strips: level 0 distributed, coarser levels replicated
+        rm = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 1000, 3))
+        cells_m, faces_m = ctx.recover_strip(ctx.row_begin, ctx.row_end)
+        gm = [None] * world; dist.all_gather_object(gm, faces_m)
+        okm = rm["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_m - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        if not okm:
+            print(f"rank {rank}: multigrid solve differs (N={Nx}x{Ny} k={k}): {rm}", flush=True)
+        ok = ok and okm
         # block-Jacobi extension (apply_preconditioner = 2) on strips: same solution as the diagonal preconditioner
         rb = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 10000, 2))
         cells_b, faces_b = ctx.recover_strip(ctx.row_begin, ctx.row_end)
@@ -48,13 +56,13 @@ def main():
         ok = ok and okb
         ctx.close()
     # fictitious-domain problem (cut cells by K2): every rank preprocesses the whole level set, assembles its strip
-    for (N, k) in [(20, 1), (24, 2)]:
+    for (N, k) in [(20, 1), (24, 2), (256, 2)]:
         mip = pb.mesh_init_params(N, N)
         hdi = pb.hho_degree_info(k + 1, k)
         ctx = make_rank_context(mip, PB.QUAD_POLY_DUNAVANT, rank, world, lr, dist)
         ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
         ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
-        res = ctx.conjugated_gradient(pb.cg_params(1e-14, 100.0, 100000, True))
+        res = ctx.conjugated_gradient(pb.cg_params(1e-14, 1e8, 100000, True))
         cells, faces = ctx.recover_strip(ctx.row_begin, ctx.row_end)
         gc = [None] * world; gf = [None] * world
         dist.all_gather_object(gc, cells); dist.all_gather_object(gf, faces)
@@ -62,13 +70,25 @@ def main():
             ref = pb.Context(lr)
             ref.mesh(mip, PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
             ref.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
-            r1 = ref.conjugated_gradient(pb.cg_params(1e-14, 100.0, 100000, True))
+            r1 = ref.conjugated_gradient(pb.cg_params(1e-14, 1e8, 100000, True))
             full = ref.recover()
             got = np.concatenate(gc + gf)
             err = np.linalg.norm(got - full) / np.linalg.norm(full)
             print(f"fictdom N={N} k={k} world={world}: iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, rel diff {err:.2e}", flush=True)
             ok = ok and err < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED
+            rm1 = ref.conjugated_gradient(pb.cg_params(1e-13, 1e8, 5000, 3)); e1 = ref.error_norms()[0]
             ref.close()
+        # the same solve with the multigrid preconditioner on the strips: same solution, same H1 error (summed over ranks), same iterations as one GPU
+        rm = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 5000, 3))
+        cells_m, faces_m = ctx.recover_strip(ctx.row_begin, ctx.row_end)
+        et = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{lr}"); dist.all_reduce(et)
+        okm = rm["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_m - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        if rank == 0:
+            okm = okm and abs(float(et[0]) - e1) <= 1e-8 * e1 and abs(rm["iterations"] - rm1["iterations"]) <= 2
+            print(f"fictdom N={N} k={k} world={world} multigrid: iterations {rm['iterations']} (1 GPU: {rm1['iterations']}), H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
+        if not okm:
+            print(f"rank {rank}: multigrid fictdom solve differs (N={N} k={k}): {rm}", flush=True)
+        ok = ok and okm
         ctx.close()
     flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
