@@ -81,3 +81,29 @@ def test_convergence_test_driver_rates(tmp_path):
             cd = k + 1; nq = ((2 * cd + 2) // 2) ** 2           # tensor Gauss points of degree 2*cd per cell
             dat = (tmp_path / f"solution_N_{N}_k_{k}.dat").read_text().splitlines()
             assert len(dat) == N * N * nq and len(dat[0].split()) == 3
+
+
+@pytest.mark.gpu
+def test_reference_loops_uncut(tmp_path):
+    """the reference's own per-cell assembly loop (convergence_test.cpp:199-247) compiled against proton_reference_api.hpp"""
+    _build()
+    for mode, k in (("uncut", 1), ("uncut-naive", 2)):
+        r = subprocess.run([os.path.join(BIN, "reference_loops"), mode, "16", str(k)], capture_output=True, text=True, check=True, cwd=tmp_path)
+        m = re.search(r"unknowns (\d+) L2 ([0-9.e+-]+) energy ([0-9.e+-]+) take_local_data_vs_sol ([0-9.e+-]+)", r.stdout)
+        assert m, r.stdout + r.stderr
+        assert int(m.group(1)) == (2 * 16 * 15) * (k + 1)
+        assert float(m.group(4)) < 1e-13
+        if mode == "uncut":      # SURVEY App. C: direct-solve errors of the restatement at N=16, k=1
+            assert abs(float(m.group(2)) - 3.5100744911e-4) < 1e-8 * 3.5e-4 * 100 and abs(float(m.group(3)) - 8.6421724735e-3) < 1e-6 * 8.6e-3
+
+
+@pytest.mark.gpu
+def test_reference_loops_cut(golden, tmp_path):
+    """run_cuthho_fictdom's loop (cuthho_square.cpp:870-900) through the per-cell API: the reference's table value"""
+    _build()
+    r = subprocess.run([os.path.join(BIN, "reference_loops"), "cut", "10", "1", "4"], capture_output=True, text=True, check=True, cwd=tmp_path)
+    m = re.search(r"cut cells (\d+) H1-error ([0-9.e+-]+)", r.stdout)
+    assert m, r.stdout + r.stderr
+    assert int(m.group(1)) == 28
+    ref = golden["cuthho_fictdom"]["k1_N10_r4"]
+    assert abs(float(m.group(2)) - ref) / ref < 5e-6
