@@ -208,6 +208,19 @@ pb_status pb_mg_info(pb_ctx* ctx, int* n_levels, double* lmax, double* setup_ms)
 pb_status pb_mg_level(pb_ctx* ctx, int level, long long dims[6], double* stencil9, double* elements16);
 pb_status pb_mg_apply(pb_ctx* ctx, const double* r, double* z);
 
+/* ---- allocation-free variant of pb_error_norms.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels,
+ * same launch and summation order, same out[3] as pb_error_norms, but the scratch (padded face vector, recovered cell dofs,
+ * per-block partial sums) lives in one file-scope device array of pb_static_scratch_bytes() = 16 MiB that every GPU loading
+ * the library holds until exit; the call performs no cudaMalloc / cudaFree and no allocating library call.  Limits: whole-mesh
+ * contexts on one GPU, plain and fictitious-domain problems, and 8*(face unknowns + cells*cbs) + 57 KiB <= 16 MiB (e.g. k=2 up
+ * to about 260 x 260 cells); beyond that PB_ERR_UNSUPPORTED with the sizes in pb_last_error.  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress): make it outside a graph capture.  All contexts of a device share
+ * the array and it keeps the last call's contents (the part that must start at zero is cleared by every call): calls that
+ * overlap on the GPU — other contexts / streams, other host threads — race on it; serialise them. ---- */
+pb_status pb_error_norms_static(pb_ctx* ctx, double out[3]);
+long long pb_static_scratch_bytes(void);
+
 /* ---- measurement hooks (bench.py): device-side timing of the last pb_assemble / pb_pcg, milliseconds ---- */
 pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg);
 /* register-resident DFMA peak probe (FP64 roofline denominator), TFLOP/s */

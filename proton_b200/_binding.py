@@ -73,6 +73,7 @@ def lib():
         L.pb_pcg_history.argtypes = [C.c_void_p, C.c_longlong]
         L.pb_pcg_get_history.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
         L.pb_sample_solution.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
+        L.pb_static_scratch_bytes.restype = C.c_longlong
         L.pb_mg_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pb_mg_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pb_mg_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -349,6 +350,10 @@ class Context:
 
     def error_norms(self):
         out = np.zeros(3); self._ck(lib().pb_error_norms(self._h, _ptr(out))); return out
+
+    def error_norms_static(self):
+        """pb_error_norms_static: the same sums without any device allocation (scratch in a 16 MiB static device array)"""
+        out = np.zeros(3); self._ck(lib().pb_error_norms_static(self._h, _ptr(out))); return out
 
     # ---- obstacle problem (apps/obstacle/obstacle.cpp)
     def obstacle_begin(self, face_degree, rhs_degree_increase=1):

@@ -664,6 +664,7 @@ static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_p
 #include "pb_api_mg.inl"
 #include "pb_api_interface_post.inl"
 #include "pb_api_obstacle.inl"
+#include "pb_api_static.inl"
 
 extern "C" pb_status pb_last_timings(pb_ctx* ctx, double* ms_local, double* ms_scatter, double* ms_pcg) {
     if (!ctx) return PB_ERR_INVALID;
