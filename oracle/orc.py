@@ -47,6 +47,11 @@ def _p(a, t=C.c_double):
     return None if a is None else a.ctypes.data_as(C.POINTER(t))
 
 
+def set_finalize(kind):
+    """0: restatement of Eigen's linear setFromTriplets (default); 1: the earlier std::sort-based build (timing comparison)"""
+    lib().orc_set_finalize(int(kind))
+
+
 def dims(cd, fd):
     out = (C.c_int * 4)()
     lib().orc_dims(cd, fd, out)

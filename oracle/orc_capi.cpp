@@ -379,3 +379,5 @@ int orc_interface_error(void* s, const double* sol, double* h1_sq) {
     ORC_CATCH(1)
 }
 }
+/* 0 = the restatement of Eigen's linear setFromTriplets (default), 1 = the earlier std::sort build (timing comparison only) */
+extern "C" void orc_set_finalize(int kind) { orc_finalize_kind = kind; }

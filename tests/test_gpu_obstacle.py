@@ -61,3 +61,20 @@ def test_obstacle_matches_reference_table_and_oracle(ctx, golden, N, k):
     assert abs(err - err_o) / err_o < 1e-8
     a, b, ia = ctx.obstacle_state()
     assert frob_rel(a, alpha_o[: N * N]) < 1e-8
+
+
+@pytest.mark.parametrize("N,k", [(64, 0), (64, 1), (128, 1)])
+def test_obstacle_table_at_64_and_128(ctx, golden, N, k):
+    """apps/obstacle/results/convergence.txt rows N = 64, 128; outer iteration counts of the oracle's saddle-system loop at N = 64
+    (15 at k = 1); the multigrid-preconditioned inner solve walks through the same active sets"""
+    ctx.mesh(pb.mesh_init_params(N, N, -1.0, 1.0, -1.0, 1.0))
+    err, iters, log = ctx.obstacle_solve(k)
+    ref = golden["obstacle"][str(N)][f"k{k}"]
+    assert abs(err - ref) / ref < 5e-6
+    if N == 64:
+        err_o, iters_o, _ = orc.obstacle_solve(N, k)
+        assert iters == iters_o and abs(err - err_o) / err_o < 1e-8
+    err_m, iters_m, log_m = ctx.obstacle_solve(k, cgp=pb.cg_params(1e-13, 1e300, 100000, 3))
+    assert iters_m == iters and abs(err_m - err) <= 1e-8 * err
+    assert [l[1] for l in log_m] == [l[1] for l in log]                 # same active-set sizes in every outer iteration
+    assert sum(l[2] for l in log_m) < sum(l[2] for l in log) / 4        # and far fewer inner iterations
