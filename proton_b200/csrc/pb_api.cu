@@ -407,12 +407,34 @@ static pb_status launch_generic(pb_ctx* ctx, const LocalArgs& A, int cd, int fd,
     *found = false; return PB_OK;
 }
 
+template <int F>
+static pb_status launch_scatter_tile(pb_ctx* ctx) {
+    constexpr int T = 32;
+    const size_t smem = sizeof(ScatterTileSmem<F, T>);
+    auto kern = scatter_tile_kernel<F, T>;
+    static int bps = 0;
+    if (!bps) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, 256, smem));
+        if (bps < 1) return fail(ctx, PB_ERR_CUDA, "scatter_tile_kernel does not fit on an SM");
+    }
+    int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
+    const long long ntiles = (ctx->nrows_blk + T - 1) / T;
+    const long long grid = std::min<long long>(ntiles, (long long)nsm * bps * 4);      // a few waves: tiles are short
+    kern<<<(unsigned)(grid < 1 ? 1 : grid), 256, smem, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
+    return PB_OK;
+}
+
 // K3: condensed blocks -> CSR values and rhs
 static pb_status scatter_system(pb_ctx* ctx) {
     const int F = ctx->F;
 #define PB_SC(F_) scatter_kernel_t<F_, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs)
     if (F == 1) scatter_packed_kernel_t<1, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
     else if (F == 2) scatter_packed_kernel_t<2, 1><<<148 * 32, 256, 0, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
+    // F = 3: tile kernel (2.02 against 2.58 ms at 2048^2, bit-identical values); F = 4 keeps the one-warp-per-row kernel, whose 28-lane
+    // rows already fill a warp (0.82 against 0.87 ms at 1024^2).  PB_SCATTER_ROWS=1 / PB_SCATTER_TILE=1 force one or the other.
+    else if (F == 3 && !getenv("PB_SCATTER_ROWS")) { pb_status st = launch_scatter_tile<3>(ctx); if (st != PB_OK) return st; }
+    else if (F == 4 && getenv("PB_SCATTER_TILE")) { pb_status st = launch_scatter_tile<4>(ctx); if (st != PB_OK) return st; }
     else if (F == 3) PB_SC(3); else if (F == 4) PB_SC(4);
     else {      // face degree > 3 (generic local kernel)
         scatter_values_kernel<<<148 * 16, 256, 0, ctx->stream>>>(ctx->nrows_blk, F, ctx->brows, ctx->brp, ctx->S, ctx->val);

@@ -277,10 +277,10 @@ static pb_status pcg_multigrid(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result*
     pcg_init_state_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, ctx->cg, ctx->hist);
     CK(cudaMemcpyAsync(ctx->d, z, (size_t)n * 8, cudaMemcpyDeviceToDevice, sm));
     CK(cudaGetLastError());
-    CgState hs{}; long long it = 0;
-    const int check_every = 2;
-    while (true) {
-        if (it > 0) {      // exit tests, beta, d = z + beta d, iter++                            (solver_cg.hpp:112-131)
+    CgState hs{};
+    // one iteration; `first` skips the direction update (d = z already)
+    auto iteration = [&](bool first) -> pb_status {
+        if (!first) {      // exit tests, beta, d = z + beta d, iter++                            (solver_cg.hpp:112-131)
             pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, z, ctx->d, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
             pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg, ctx->hist, ctx->hist_cap);
         }
@@ -294,12 +294,38 @@ static pb_status pcg_multigrid(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result*
         mg_dot_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->r, z, p_rz, nullptr, ctx->cg);
         { pb_status st = reduce1(nblk, p_rz, s_rz); if (st != PB_OK) return st; }
         CK(cudaGetLastError());
-        if (++it % check_every == 0) {
-            CK(cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, sm));
-            CK(cudaStreamSynchronize(sm));
-            if (hs.done) break;
-        }
+        return PB_OK;
+    };
+    { pb_status st = iteration(true); if (st != PB_OK) return st; }
+    // An iteration is ~100 launches (12 vertex levels, most of them tiny) and carries no host state: batches of `check_every`
+    // iterations are captured once into a CUDA graph (NCCL's send/recv and all-reduces included on several ranks) and
+    // replayed; the host polls the exit flag between batches, the kernels of an overshooting batch return on `done`.
+    // check_every must be EVEN: a V-cycle swaps the two sweep buffers of every vertex level (host pointers), and a graph
+    // bakes pointers in — after an even number of cycles the host state is back where the capture started.
+    const int check_every = 2;
+    cudaGraph_t graph = nullptr; cudaGraphExec_t gexec = nullptr;
+    if (!getenv("PB_PCG_NO_GRAPH")) {
+        CK(cudaStreamBeginCapture(sm, cudaStreamCaptureModeThreadLocal));
+        pb_status cst = PB_OK;
+        for (int k = 0; k < check_every && cst == PB_OK; k++) cst = iteration(false);
+        cudaError_t ce = cudaStreamEndCapture(sm, &graph);      // always closes the capture, also on the error path
+        if (cst != PB_OK) { if (graph) cudaGraphDestroy(graph); return cst; }
+        CK(ce);
+        cudaError_t ie = cudaGraphInstantiate(&gexec, graph, 0);
+        if (ie != cudaSuccess) { cudaGraphDestroy(graph); return fail(ctx, PB_ERR_CUDA, "pb_pcg: cudaGraphInstantiate failed: %s", cudaGetErrorString(ie)); }
     }
+    pb_status lst = PB_OK;
+    while (lst == PB_OK) {
+        if (gexec) { cudaError_t le = cudaGraphLaunch(gexec, sm); if (le != cudaSuccess) { lst = fail(ctx, PB_ERR_CUDA, "pb_pcg: cudaGraphLaunch failed: %s", cudaGetErrorString(le)); break; } }
+        else for (int k = 0; k < check_every && lst == PB_OK; k++) lst = iteration(false);
+        if (lst != PB_OK) break;
+        cudaError_t me = cudaMemcpyAsync(&hs, ctx->cg, sizeof hs, cudaMemcpyDeviceToHost, sm);
+        if (me == cudaSuccess) me = cudaStreamSynchronize(sm);
+        if (me != cudaSuccess) { lst = fail(ctx, PB_ERR_CUDA, "pb_pcg: %s", cudaGetErrorString(me)); break; }
+        if (hs.done) break;
+    }
+    if (gexec) { cudaGraphExecDestroy(gexec); cudaGraphDestroy(graph); }
+    if (lst != PB_OK) return lst;
     CK(cudaEventRecord(ctx->ev[1], sm)); CK(cudaStreamSynchronize(sm));
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->ms_pcg = ms;
     ctx->hist_n = ctx->hist ? std::min<long long>(hs.iters + 2, ctx->hist_cap) : 0;

@@ -232,6 +232,102 @@ __global__ void __launch_bounds__(256) scatter_packed_kernel_t(long long nrows_b
     }
 }
 
+// values + rhs, tile version (F = 2..4): a block of 256 threads owns T consecutive block rows.  Every S chunk a block row needs
+// (the F columns of the face inside each of its two cells: F*NF contiguous doubles, 16-byte aligned) is read exactly once in
+// the whole launch, so the read side is already minimal; what the one-warp-per-row kernel above loses is (a) memory-level
+// parallelism — record -> chunk -> store are three dependent round trips per warp — and (b) sector fills: a block row's
+// nb*F*F*8 bytes (504 at k = 2) start and end inside 32-byte sectors that another warp completes later, and ncu showed
+// 0.77 GB of DRAM reads beyond the 5.77 GB the kernel asks for.  Here the records arrive as one coalesced copy, all 2T chunks
+// are in flight together as 16-byte cp.async copies into shared memory, the tile's values are formed in shared memory and leave
+// as ONE contiguous, fully coalesced span [brp[br0], brp[br0+T]) * F*F (16 KB at k = 2): only the two ends of a span are partial
+// sectors.  Tiles that contain rows the interface problem fills elsewhere (nb = 0, or a span longer than nb blocks) take the
+// per-row path, which writes exactly the entries scatter_kernel_t writes.
+PB_D void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+PB_D void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
+template <int F, int T>
+struct ScatterTileSmem {
+    static constexpr int NF = 4 * F, CH = F * NF;          // doubles per chunk
+    double chunk[T][2][CH];
+    double outv[T * 7 * F * F];
+    double rhsv[T * F];
+    long long off[T + 1];
+    BlockRow rec[T];
+    int regular;
+};
+
+template <int F, int T>
+__global__ void __launch_bounds__(256) scatter_tile_kernel(long long nrows_blk, const BlockRow* __restrict__ rows, const long long* __restrict__ brp,
+                                                           const double* __restrict__ S, const double* __restrict__ g,
+                                                           double* __restrict__ val, double* __restrict__ rhs) {
+    using SM = ScatterTileSmem<F, T>;
+    constexpr int NF = 4 * F, CH = SM::CH, V = CH / 2;      // V 16-byte vectors per chunk
+    static_assert(sizeof(BlockRow) % 4 == 0 && CH % 2 == 0, "records are copied as ints, chunks as double2");
+    extern __shared__ __align__(16) unsigned char scatter_smem_raw[];
+    SM& s = *reinterpret_cast<SM*>(scatter_smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long ntiles = (nrows_blk + T - 1) / T;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long br0 = tile * T;
+        const int cnt = (int)(nrows_blk - br0 < T ? nrows_blk - br0 : T);
+        // records and offsets: contiguous in memory
+        {
+            const int* src = reinterpret_cast<const int*>(rows + br0); int* dst = reinterpret_cast<int*>(s.rec);
+            for (int i = tid; i < cnt * (int)(sizeof(BlockRow) / 4); i += 256) dst[i] = src[i];
+            for (int i = tid; i <= cnt; i += 256) s.off[i] = brp[br0 + i];
+            if (tid == 0) s.regular = 1;
+        }
+        __syncthreads();
+        // all chunks of the tile in flight at once
+        for (int i = tid; i < cnt * 2 * V; i += 256) {
+            const int t = i / (2 * V), r = i - t * (2 * V), k = r / V, v = r - k * V;
+            const BlockRow& R = s.rec[t];
+            const double* src = S + (long long)R.cell[k] * (NF * NF) + R.li[k] * CH + 2 * v;
+            cp_async16(&s.chunk[t][k][2 * v], src);
+        }
+        for (int i = tid; i < cnt * F; i += 256) {
+            const int t = i / F, a = i - t * F;
+            const BlockRow& R = s.rec[t];
+            s.rhsv[i] = g[(long long)R.cell[0] * NF + R.li[0] * F + a] + g[(long long)R.cell[1] * NF + R.li[1] * F + a];
+        }
+        for (int t = tid; t < cnt; t += 256)
+            if (s.rec[t].nb == 0 || s.off[t + 1] - s.off[t] != s.rec[t].nb) s.regular = 0;      // benign race: every writer stores 0
+        cp_async_wait_all();
+        __syncthreads();
+        const bool regular = s.regular != 0;
+        const long long base = s.off[0] * (F * F);
+        // lane = position (b, bc) inside a scalar row; the transposed entry is read so that bc runs over contiguous doubles (S is
+        // symmetric up to rounding), exactly the sums of scatter_kernel_t
+        const int b = lane / F, bc = lane - b * F;
+        for (int t = warp; t < cnt; t += 8) {
+            const BlockRow& R = s.rec[t];
+            const int rowlen = R.nb * F;
+            if (lane < rowlen) {
+                const int l0 = R.src[0][b], l1 = R.src[1][b];
+                const long long o = s.off[t] * (F * F) - base;
+#pragma unroll
+                for (int a = 0; a < F; a++) {
+                    double v0 = 0.0, v1 = 0.0;
+                    if (l0 != 255) v0 = s.chunk[t][0][a * NF + l0 * F + bc];
+                    if (l1 != 255) v1 = s.chunk[t][1][a * NF + l1 * F + bc];
+                    if (regular) s.outv[o + a * rowlen + lane] = v0 + v1;
+                    else val[base + o + a * rowlen + lane] = v0 + v1;
+                }
+            }
+        }
+        __syncthreads();
+        if (regular) {
+            const int nout = (int)(s.off[cnt] * (F * F) - base);
+            for (int i = tid; i < nout; i += 256) val[base + i] = s.outv[i];
+        }
+        for (int i = tid; i < cnt * F; i += 256) rhs[br0 * F + i] = s.rhsv[i];
+        __syncthreads();
+    }
+}
+
 // rhs: one thread per scalar row; g is [cell][NF] (already Dirichlet-lifted)
 __global__ void scatter_rhs_kernel(long long nrows_blk, int F, const BlockRow* rows, const double* __restrict__ g, double* __restrict__ rhs) {
     long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;

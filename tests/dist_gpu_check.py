@@ -19,6 +19,12 @@ def main():
     rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    def global_close(a, b, tol=1e-8):
+        """|a - b| <= tol |b| over ALL ranks: a strip that lies outside the cut domain holds an identically zero solution"""
+        t = torch.tensor([float(np.sum((a - b) ** 2)), float(np.sum(b ** 2))], dtype=torch.float64, device=f"cuda:{lr}")
+        dist.all_reduce(t)
+        return float(t[0]) ** 0.5 <= tol * float(t[1]) ** 0.5 + 1e-13
+
     ok = True
     for (Nx, Ny, k) in [(16, 16, 1), (24, 19, 2), (12, 32, 0)]:
         mip = pb.mesh_init_params(Nx, Ny)
@@ -43,14 +49,14 @@ def main():
         rm = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 1000, 3))
         cells_m, faces_m = ctx.recover_strip(ctx.row_begin, ctx.row_end)
         gm = [None] * world; dist.all_gather_object(gm, faces_m)
-        okm = rm["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_m - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        okm = rm["exit_reason"] == PB.CG_CONVERGED and global_close(faces_m, faces)
         if not okm:
             print(f"rank {rank}: multigrid solve differs (N={Nx}x{Ny} k={k}): {rm}", flush=True)
         ok = ok and okm
         # block-Jacobi extension (apply_preconditioner = 2) on strips: same solution as the diagonal preconditioner
         rb = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e6, 10000, 2))
         cells_b, faces_b = ctx.recover_strip(ctx.row_begin, ctx.row_end)
-        okb = rb["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_b - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        okb = rb["exit_reason"] == PB.CG_CONVERGED and global_close(faces_b, faces)
         if not okb:
             print(f"rank {rank}: block-Jacobi solve differs (N={Nx}x{Ny} k={k}): {rb}", flush=True)
         ok = ok and okb
@@ -82,7 +88,7 @@ def main():
         rm = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 5000, 3))
         cells_m, faces_m = ctx.recover_strip(ctx.row_begin, ctx.row_end)
         et = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{lr}"); dist.all_reduce(et)
-        okm = rm["exit_reason"] == PB.CG_CONVERGED and np.linalg.norm(faces_m - faces) <= 1e-8 * np.linalg.norm(faces) + 1e-13
+        okm = rm["exit_reason"] == PB.CG_CONVERGED and global_close(faces_m, faces)
         if rank == 0:
             okm = okm and abs(float(et[0]) - e1) <= 1e-8 * e1 and abs(rm["iterations"] - rm1["iterations"]) <= 2
             print(f"fictdom N={N} k={k} world={world} multigrid: iterations {rm['iterations']} (1 GPU: {rm1['iterations']}), H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
