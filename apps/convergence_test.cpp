@@ -41,6 +41,8 @@ static bool read_config(const char* fn, convergence_test_params& ctp) {
 int main(int argc, char** argv) {
     convergence_test_params ctp;
     if (argc >= 2 && !read_config(argv[1], ctp)) { std::cout << "Problems opening configuration file" << std::endl; return 1; }
+    if (ctp.direct)     // convergence_test.cpp:222-228 solves with Eigen::SparseLU when `direct = true`; there is no sparse LU on the device path
+        std::cout << "Note: `direct = true` is ignored: the solve is conjugated_gradient at 1e-12 (no sparse direct solver on the GPU path)" << std::endl;
     try {
         for (size_t k = ctp.deg_min; k <= ctp.deg_max; k++) {
             std::cout << "Testing degree " << k << ". Expected rates: L2 " << k + 2 << ", energy " << k + 1 << std::endl;

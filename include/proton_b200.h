@@ -85,18 +85,24 @@ pb_status pb_mesh_compress_table(pb_ctx* ctx, long long* table);
  * `radius` centred (cx, cy), kind 1 = horizontal line y = cut_y.
  * pb_cut_preprocess: detect_node_position, detect_cut_faces, move_nodes, detect_cut_faces, detect_cut_cells,
  * refine_interface(refine_steps) in the order of cuthho_square.cpp:2030-2052 (src/methods/cuthho_bits/
- * cuthho_geom.hpp:118-161, 275-340, 466-543, 609-673), on the device.  Moves mesh points.  The reference throws
+ * cuthho_geom.hpp:118-161, 275-340, 466-543, 609-673), on the device.  Moves mesh points.  refine_steps <= 6 (the reference's -r is
+ * uncapped and its table has r = 7 rows: PB_ERR_UNSUPPORTED here; pb_cut_upload has the same limit of 65 points per cell).  The reference throws
  * for >2 cuts per cell, concave displaced cells or a lost interface: PB_ERR_INVALID with the same message.
  * pb_cut_upload: the same user data computed by the caller (all arrays for the WHOLE mesh; iface_off has
  * ncells+1 entries, every cut cell must carry the same number of interface points).
  * pb_cut_download: read the device-side user data back (any pointer may be NULL); iface_xy receives, cell by
- * cell in ascending order, the interface polylines; *n_iface_pts the number of points per cut cell. ---- */
+ * cell in ascending order, the interface polylines; *n_iface_pts the number of points per cut cell.
+ * A strip context (one rank of a multi-GPU job) classifies and keeps ONLY the rows it needs — its own cell rows, the ghost row below,
+ * their faces and vertices — so preprocessing costs each rank its share: pb_mesh_get_points returns displaced points for those rows,
+ * pb_cut_download fills the rest of the whole-mesh arrays with PB_UNDEF / zeros, *n_cut_cells and iface_xy cover the cut cells of
+ * those rows.  pb_cut_counts: cut cells held (ghost row included) and cut cells of the OWNED rows (sum it over the ranks). ---- */
 pb_status pb_cut_levelset(pb_ctx* ctx, int kind, double radius, double cx, double cy, double cut_y);
 pb_status pb_cut_preprocess(pb_ctx* ctx, int refine_steps);
 pb_status pb_cut_upload(pb_ctx* ctx, const int* node_location, const int* face_location, const double* face_intersection_xy,
                         const int* cell_location, const long long* iface_off, const double* iface_xy);
 pb_status pb_cut_download(pb_ctx* ctx, int* node_location, int* face_location, double* face_intersection_xy, int* cell_location,
                           long long* n_cut_cells, int* n_iface_pts, double* iface_xy);
+pb_status pb_cut_counts(pb_ctx* ctx, long long* n_cut_cells_held, long long* n_cut_cells_owned);
 
 /* ---- stages 1+2: the drivers' per-cell loop (make_hho_laplacian + make_hho_*_stabilization + make_rhs, then
  * static condensation) and assembler.assemble()/finalize() (hho.hpp:344-406, 451-455) onto the condensed face

@@ -215,6 +215,12 @@ class Context:
         self._ck(lib().pb_cut_download(self._h, None, None, None, None, None, None, _ptr(pts)))
         return dict(node_loc=nl, face_loc=fl, face_ip=fip, cell_loc=cl, iface_pts=pts)
 
+    def cut_counts_owned(self):
+        """(cut cells this context holds, ghost row included; cut cells of its OWNED rows)"""
+        a = C.c_longlong(); b = C.c_longlong()
+        self._ck(lib().pb_cut_counts(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def cut_counts(self):
         """(number of cut cells, interface points per cut cell) of the last preprocessing"""
         ncut = C.c_longlong(); ni = C.c_int()

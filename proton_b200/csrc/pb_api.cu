@@ -5,6 +5,7 @@
 #include <cub/device/device_reduce.cuh>
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -40,9 +41,13 @@ struct pb_ctx {
     StiffEnt* stiff_tab = nullptr; int stiff_key = -1;      // K1: stiff_table of the last reconstruction degree
     // cutHHO user data (whole mesh)
     LevelSet ls{}; bool have_ls = false, have_cut = false;
+    // node_loc / face_loc / face_ip / cell_loc_g are indexed by GLOBAL point / face / cell id but only hold the window of rows this
+    // context needs (cut_window, pb_api_cut.inl): the pointers are the allocations (*_a) shifted back by the window start
     int *node_loc = nullptr, *face_loc = nullptr, *cell_loc_g = nullptr, *cut_cells = nullptr;
     double2 *face_ip = nullptr, *iface = nullptr;
-    int ncut = 0, NI = 0;
+    int *node_loc_a = nullptr, *face_loc_a = nullptr, *cell_loc_a = nullptr; double2* face_ip_a = nullptr;
+    long long pw0 = 0, pw1 = 0, fw0 = 0, fw1 = 0, cw0 = 0, cw1 = 0;      // windows [w0, w1) of point, face and cell ids
+    int ncut = 0, NI = 0, ncut_owned = 0;
     long long nfaces = 0;
     // assembly
     bool assembled = false;
@@ -181,8 +186,9 @@ static void free_system(pb_ctx* c) {
 
 static void dist_release(pb_ctx* c);      // pb_api_dist.inl
 static void free_cut(pb_ctx* c) {
-    dfree(&c->node_loc); dfree(&c->face_loc); dfree(&c->cell_loc_g); dfree(&c->cut_cells); dfree(&c->face_ip); dfree(&c->iface);
-    c->have_cut = false; c->ncut = 0; c->NI = 0;
+    dfree(&c->node_loc_a); dfree(&c->face_loc_a); dfree(&c->cell_loc_a); dfree(&c->face_ip_a); dfree(&c->cut_cells); dfree(&c->iface);
+    c->node_loc = c->face_loc = c->cell_loc_g = nullptr; c->face_ip = nullptr;
+    c->have_cut = false; c->ncut = 0; c->NI = 0; c->ncut_owned = 0;
 }
 
 extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {

@@ -9,9 +9,32 @@ extern "C" pb_status pb_cut_levelset(pb_ctx* ctx, int kind, double radius, doubl
     return PB_OK;
 }
 
+// rows of the mesh this context needs cut data for.  Cells: its local cells (own rows + the ghost row below).  Faces: the face
+// rows of those cells and the row above them (top faces of the last cell row; a face row holds the bottom and vertical faces of a
+// cell row).  Points: the vertex rows of those faces.  A whole-mesh context gets the whole mesh.
+static void cut_window(pb_ctx* ctx) {
+    const Grid& g = ctx->grid;
+    const long long r0 = ctx->strip.cell_row0, r1 = g.row_end;
+    ctx->cw0 = r0 * g.Nx; ctx->cw1 = r1 * g.Nx;
+    ctx->fw0 = r0 * (2 * g.Nx + 1); ctx->fw1 = r1 < g.Ny ? (r1 + 1) * (2 * g.Nx + 1) : ctx->nfaces;
+    ctx->pw0 = r0 * (g.Nx + 1); ctx->pw1 = std::min(r1 + 2, g.Ny + 1) * (g.Nx + 1);
+}
 static pb_status alloc_cut_arrays(pb_ctx* ctx) {
-    CK(dalloc(ctx, &ctx->node_loc, (size_t)ctx->npoints)); CK(dalloc(ctx, &ctx->face_loc, (size_t)ctx->nfaces));
-    CK(dalloc(ctx, &ctx->face_ip, (size_t)ctx->nfaces)); CK(dalloc(ctx, &ctx->cell_loc_g, (size_t)ctx->ncells_global));
+    cut_window(ctx);
+    CK(dalloc(ctx, &ctx->node_loc_a, (size_t)(ctx->pw1 - ctx->pw0))); CK(dalloc(ctx, &ctx->face_loc_a, (size_t)(ctx->fw1 - ctx->fw0)));
+    CK(dalloc(ctx, &ctx->face_ip_a, (size_t)(ctx->fw1 - ctx->fw0))); CK(dalloc(ctx, &ctx->cell_loc_a, (size_t)(ctx->cw1 - ctx->cw0)));
+    ctx->node_loc = ctx->node_loc_a - ctx->pw0; ctx->face_loc = ctx->face_loc_a - ctx->fw0;
+    ctx->face_ip = ctx->face_ip_a - ctx->fw0; ctx->cell_loc_g = ctx->cell_loc_a - ctx->cw0;
+    return PB_OK;
+}
+// cut cells of the OWNED rows among the (ascending) list of the window: everything from the first cell of row_begin on
+static pb_status count_owned_cut(pb_ctx* ctx) {
+    ctx->ncut_owned = 0;
+    if (ctx->ncut == 0) return PB_OK;
+    std::vector<int> h((size_t)ctx->ncut);
+    CK(cudaMemcpy(h.data(), ctx->cut_cells, (size_t)ctx->ncut * 4, cudaMemcpyDeviceToHost));
+    const long long first = ctx->grid.row_begin * ctx->grid.Nx;
+    ctx->ncut_owned = (int)(h.end() - std::lower_bound(h.begin(), h.end(), (int)first));
     return PB_OK;
 }
 
@@ -25,28 +48,42 @@ static const char* cut_error_text(int e) {
 extern "C" pb_status pb_cut_preprocess(pb_ctx* ctx, int refine_steps) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->have_mesh && ctx->have_ls, PB_ERR_STATE, "pb_cut_preprocess: needs a mesh and pb_cut_levelset");
-    NEED(refine_steps >= 0 && refine_steps <= 6, PB_ERR_INVALID, "pb_cut_preprocess: refine_steps must be in [0, 6]");
+    NEED(refine_steps >= 0, PB_ERR_INVALID, "pb_cut_preprocess: negative refine_steps");
+    NEED(refine_steps <= 6, PB_ERR_UNSUPPORTED, "pb_cut_preprocess: refine_steps > 6 is not built (the cut-cell kernels hold the 2^r + 1 interface points of a cell in shared memory; the reference's -r is uncapped)");
     CK(cudaSetDevice(ctx->device));
     free_cut(ctx);
     pb_status st = alloc_cut_arrays(ctx); if (st != PB_OK) return st;
     const Grid& g = ctx->grid; const LevelSet L = ctx->ls;
-    const long long np = ctx->npoints, nf = ctx->nfaces, nc = ctx->ncells_global;
     cudaStream_t sm = ctx->stream;
-    double* disp = nullptr; int *displaced = nullptr, *is_cut = nullptr, *slot = nullptr, *err = nullptr; double2* p01 = nullptr;
+    // windows (global ids).  The node displacement of move_nodes gathers from the faces around a node, so the FIRST face pass and
+    // the displacement pass run one face row further out on both sides; everything else runs on the windows of cut_window().
+    const long long pw0 = ctx->pw0, pw1 = ctx->pw1, fw0 = ctx->fw0, fw1 = ctx->fw1, cw0 = ctx->cw0, cw1 = ctx->cw1;
+    const long long r0 = ctx->strip.cell_row0, r1 = g.row_end;
+    const long long fh0 = (r0 > 0 ? r0 - 1 : 0) * (2 * g.Nx + 1), fh1 = r1 + 2 <= g.Ny ? (r1 + 2) * (2 * g.Nx + 1) : ctx->nfaces;      // first-pass faces
+    const long long np = pw1 - pw0, nc = cw1 - cw0, nfh = fh1 - fh0;
+    double* disp = nullptr; int *displaced = nullptr, *is_cut = nullptr, *slot = nullptr, *err = nullptr; double2* p01 = nullptr; void* tmp = nullptr;
+    int* floc1 = nullptr; double2* fip1 = nullptr;      // first-pass face data (window + halo rows)
+    // temporaries are released on every exit, error paths included
+    struct Cleanup { std::vector<void**> v; ~Cleanup() { for (void** q : v) if (*q) { cudaFree(*q); *q = nullptr; } } } cleanup;
+    cleanup.v = {(void**)&disp, (void**)&displaced, (void**)&is_cut, (void**)&slot, (void**)&err, (void**)&p01, &tmp, (void**)&floc1, (void**)&fip1};
     CK(cudaMalloc((void**)&disp, (size_t)np * 16)); CK(cudaMalloc((void**)&displaced, (size_t)np * 4));
     CK(cudaMalloc((void**)&is_cut, (size_t)(nc + 1) * 4)); CK(cudaMalloc((void**)&slot, (size_t)(nc + 1) * 4));
     CK(cudaMalloc((void**)&err, 4)); CK(cudaMalloc((void**)&p01, (size_t)nc * 32));
+    CK(cudaMalloc((void**)&floc1, (size_t)nfh * 4)); CK(cudaMalloc((void**)&fip1, (size_t)nfh * 16));
     CK(cudaMemsetAsync(disp, 0, (size_t)np * 16, sm)); CK(cudaMemsetAsync(displaced, 0, (size_t)np * 4, sm));
     CK(cudaMemsetAsync(err, 0, 4, sm)); CK(cudaMemsetAsync(is_cut, 0, (size_t)(nc + 1) * 4, sm));
+    // the temporaries are indexed by global ids too: shift them back by their window start
+    double* disp_g = disp - 2 * pw0; int* displaced_g = displaced - pw0; int* is_cut_g = is_cut - cw0; int* slot_g = slot - cw0; double2* p01_g = p01 - 2 * cw0;
+    int* floc1_g = floc1 - fh0; double2* fip1_g = fip1 - fh0;
     const int B = 256, G = 148 * 8;
-    cut_node_position_kernel<<<G, B, 0, sm>>>(L, np, ctx->points, ctx->node_loc);
-    cut_faces_kernel<<<G, B, 0, sm>>>(L, g, nf, ctx->points, ctx->face_loc, ctx->face_ip);
-    cut_displacements_kernel<<<G, B, 0, sm>>>(g, nf, ctx->points, ctx->face_loc, ctx->face_ip, disp, displaced);
-    cut_apply_displacements_kernel<<<G, B, 0, sm>>>(np, ctx->points, disp, displaced);
-    cut_faces_kernel<<<G, B, 0, sm>>>(L, g, nf, ctx->points, ctx->face_loc, ctx->face_ip);          // cuthho_square.cpp:2048
-    cut_cells_kernel<<<G, B, 0, sm>>>(L, g, nc, ctx->points, displaced, ctx->face_loc, ctx->face_ip, ctx->cell_loc_g, p01, is_cut, err);
+    cut_node_position_kernel<<<G, B, 0, sm>>>(L, pw0, pw1, ctx->points, ctx->node_loc);
+    cut_faces_kernel<<<G, B, 0, sm>>>(L, g, fh0, fh1, ctx->points, floc1_g, fip1_g);
+    cut_displacements_kernel<<<G, B, 0, sm>>>(g, fh0, fh1, pw0, pw1, ctx->points, floc1_g, fip1_g, disp_g, displaced_g);
+    cut_apply_displacements_kernel<<<G, B, 0, sm>>>(pw0, pw1, ctx->points, disp_g, displaced_g);
+    cut_faces_kernel<<<G, B, 0, sm>>>(L, g, fw0, fw1, ctx->points, ctx->face_loc, ctx->face_ip);          // cuthho_square.cpp:2048
+    cut_cells_kernel<<<G, B, 0, sm>>>(L, g, cw0, cw1, ctx->points, displaced_g, ctx->face_loc, ctx->face_ip, ctx->cell_loc_g, p01_g, is_cut_g, err);
     CK(cudaGetLastError());
-    void* tmp = nullptr; size_t tmpb = 0;
+    size_t tmpb = 0;
     CK(cub::DeviceScan::ExclusiveSum(nullptr, tmpb, is_cut, slot, (int)(nc + 1), sm));
     CK(cudaMalloc(&tmp, tmpb));
     CK(cub::DeviceScan::ExclusiveSum(tmp, tmpb, is_cut, slot, (int)(nc + 1), sm));
@@ -60,15 +97,15 @@ extern "C" pb_status pb_cut_preprocess(pb_ctx* ctx, int refine_steps) {
         ctx->ncut = ncut; ctx->NI = (1 << refine_steps) + 1;
         CK(dalloc(ctx, &ctx->cut_cells, (size_t)ncut)); CK(dalloc(ctx, &ctx->iface, (size_t)ncut * ctx->NI));
         if (ncut > 0) {
-            cut_compact_kernel<<<G, B, 0, sm>>>(nc, is_cut, slot, ctx->cut_cells);
-            cut_refine_kernel<<<(ncut + 127) / 128, 128, 0, sm>>>(L, g, ncut, ctx->NI, ctx->cut_cells, ctx->points, p01, ctx->iface, err);
+            cut_compact_kernel<<<G, B, 0, sm>>>(cw0, cw1, is_cut_g, slot_g, ctx->cut_cells);
+            cut_refine_kernel<<<(ncut + 127) / 128, 128, 0, sm>>>(L, g, ncut, ctx->NI, ctx->cut_cells, ctx->points, p01_g, ctx->iface, err);
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(&herr, err, 4, cudaMemcpyDeviceToHost, sm));
             CK(cudaStreamSynchronize(sm));
             if (herr) rc = fail(ctx, PB_ERR_INVALID, "pb_cut_preprocess: %s", cut_error_text(herr));
         }
+        if (rc == PB_OK) rc = count_owned_cut(ctx);
     }
-    cudaFree(tmp); cudaFree(disp); cudaFree(displaced); cudaFree(is_cut); cudaFree(slot); cudaFree(err); cudaFree(p01);
     ctx->have_cut = rc == PB_OK; ctx->assembled = false; ctx->ifc_struct_ok = false;
     return rc;
 }
@@ -81,26 +118,27 @@ extern "C" pb_status pb_cut_upload(pb_ctx* ctx, const int* node_location, const 
     CK(cudaSetDevice(ctx->device));
     free_cut(ctx);
     pb_status st = alloc_cut_arrays(ctx); if (st != PB_OK) return st;
-    const long long nc = ctx->ncells_global;
     std::vector<int> cells; std::vector<double> pts; int NI = 0;
-    for (long long c = 0; c < nc; c++) {
+    for (long long c = ctx->cw0; c < ctx->cw1; c++) {      // the caller passes whole-mesh arrays; a strip context keeps its window
         const long long n = iface_off[c + 1] - iface_off[c];
         if (cell_location[c] != PB_ON_INTERFACE) continue;
         if (NI == 0) NI = (int)n;
         NEED(n == NI && n >= 2, PB_ERR_INVALID, "pb_cut_upload: every cut cell must carry the same number (>= 2) of interface points");
+        NEED(n <= 65, PB_ERR_UNSUPPORTED, "pb_cut_upload: more than 65 interface points per cell (refine_steps > 6) are not built");
         cells.push_back((int)c);
         pts.insert(pts.end(), iface_xy + 2 * iface_off[c], iface_xy + 2 * iface_off[c + 1]);
     }
     ctx->ncut = (int)cells.size(); ctx->NI = NI;
-    CK(cudaMemcpy(ctx->node_loc, node_location, (size_t)ctx->npoints * 4, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->face_loc, face_location, (size_t)ctx->nfaces * 4, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->face_ip, face_ip_xy, (size_t)ctx->nfaces * 16, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(ctx->cell_loc_g, cell_location, (size_t)nc * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->node_loc_a, node_location + ctx->pw0, (size_t)(ctx->pw1 - ctx->pw0) * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->face_loc_a, face_location + ctx->fw0, (size_t)(ctx->fw1 - ctx->fw0) * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->face_ip_a, face_ip_xy + 2 * ctx->fw0, (size_t)(ctx->fw1 - ctx->fw0) * 16, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->cell_loc_a, cell_location + ctx->cw0, (size_t)(ctx->cw1 - ctx->cw0) * 4, cudaMemcpyHostToDevice));
     CK(dalloc(ctx, &ctx->cut_cells, cells.size())); CK(dalloc(ctx, &ctx->iface, pts.size() / 2));
     if (!cells.empty()) {
         CK(cudaMemcpy(ctx->cut_cells, cells.data(), cells.size() * 4, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(ctx->iface, pts.data(), pts.size() * 8, cudaMemcpyHostToDevice));
     }
+    { pb_status st = count_owned_cut(ctx); if (st != PB_OK) return st; }
     ctx->have_cut = true; ctx->assembled = false; ctx->ifc_struct_ok = false;
     return PB_OK;
 }
@@ -110,13 +148,21 @@ extern "C" pb_status pb_cut_download(pb_ctx* ctx, int* node_location, int* face_
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->have_cut, PB_ERR_STATE, "pb_cut_download: no cut data");
     CK(cudaSetDevice(ctx->device));
-    if (node_location) CK(cudaMemcpy(node_location, ctx->node_loc, (size_t)ctx->npoints * 4, cudaMemcpyDeviceToHost));
-    if (face_location) CK(cudaMemcpy(face_location, ctx->face_loc, (size_t)ctx->nfaces * 4, cudaMemcpyDeviceToHost));
-    if (face_ip_xy) CK(cudaMemcpy(face_ip_xy, ctx->face_ip, (size_t)ctx->nfaces * 16, cudaMemcpyDeviceToHost));
-    if (cell_location) CK(cudaMemcpy(cell_location, ctx->cell_loc_g, (size_t)ctx->ncells_global * 4, cudaMemcpyDeviceToHost));
+    // whole-mesh host arrays; outside the rows this context holds: PB_UNDEF / zero points
+    if (node_location) { std::fill(node_location, node_location + ctx->npoints, (int)PB_UNDEF); CK(cudaMemcpy(node_location + ctx->pw0, ctx->node_loc_a, (size_t)(ctx->pw1 - ctx->pw0) * 4, cudaMemcpyDeviceToHost)); }
+    if (face_location) { std::fill(face_location, face_location + ctx->nfaces, (int)PB_UNDEF); CK(cudaMemcpy(face_location + ctx->fw0, ctx->face_loc_a, (size_t)(ctx->fw1 - ctx->fw0) * 4, cudaMemcpyDeviceToHost)); }
+    if (face_ip_xy) { std::fill(face_ip_xy, face_ip_xy + 2 * ctx->nfaces, 0.0); CK(cudaMemcpy(face_ip_xy + 2 * ctx->fw0, ctx->face_ip_a, (size_t)(ctx->fw1 - ctx->fw0) * 16, cudaMemcpyDeviceToHost)); }
+    if (cell_location) { std::fill(cell_location, cell_location + ctx->ncells_global, (int)PB_UNDEF); CK(cudaMemcpy(cell_location + ctx->cw0, ctx->cell_loc_a, (size_t)(ctx->cw1 - ctx->cw0) * 4, cudaMemcpyDeviceToHost)); }
     if (n_cut_cells) *n_cut_cells = ctx->ncut;
     if (n_iface_pts) *n_iface_pts = ctx->NI;
     if (iface_xy && ctx->ncut > 0) CK(cudaMemcpy(iface_xy, ctx->iface, (size_t)ctx->ncut * ctx->NI * 16, cudaMemcpyDeviceToHost));   // cut list is in ascending cell order
+    return PB_OK;
+}
+
+extern "C" pb_status pb_cut_counts(pb_ctx* ctx, long long* n_window, long long* n_owned) {
+    if (!ctx) return PB_ERR_INVALID;
+    NEED(ctx->have_cut, PB_ERR_STATE, "pb_cut_counts: no cut data");
+    if (n_window) *n_window = ctx->ncut; if (n_owned) *n_owned = ctx->ncut_owned;
     return PB_OK;
 }
 

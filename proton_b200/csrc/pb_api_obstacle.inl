@@ -37,6 +37,7 @@ extern "C" pb_status pb_obstacle_iterate(pb_ctx* ctx, const pb_cg_params* cgp, d
     Grid g = ctx->grid; g.row_begin = ctx->strip.cell_row0;
     const int B = 128, G = 148 * 8;
     int* d_act = nullptr; double* parts = nullptr;
+    struct Cleanup { int** a; double** b; ~Cleanup() { if (*a) cudaFree(*a); if (*b) cudaFree(*b); } } cleanup{&d_act, &parts};      // also on the error paths
     CK(cudaMalloc((void**)&d_act, 4)); CK(cudaMalloc((void**)&parts, (size_t)G * 8));
     CK(cudaMemsetAsync(d_act, 0, 4, ctx->stream));
     if (fd == 0) obstacle_condense_kernel<0><<<G, B, 0, ctx->stream>>>(g, nc, ctx->points, ctx->lc, ctx->rhsloc, ctx->ob_alpha, ctx->ob_beta, ctx->ob_gamma, 1.0, ctx->prm.fun, ctx->ob_inA, ctx->S, ctx->g, d_act);
@@ -54,7 +55,6 @@ extern "C" pb_status pb_obstacle_iterate(pb_ctx* ctx, const pb_cg_params* cgp, d
     CK(cudaGetLastError());
     d2 += sum_parts(ctx, parts, G, &e); CK(e);
     int act = 0; CK(cudaMemcpy(&act, d_act, 4, cudaMemcpyDeviceToHost));
-    cudaFree(d_act); cudaFree(parts);
     // the Dirichlet-face entries of alpha change only in the first outer iteration (0 -> projection), where the
     // reference cannot stop either; they are left out of the norm
     if (delta_alpha_norm) *delta_alpha_norm = std::sqrt(d2);

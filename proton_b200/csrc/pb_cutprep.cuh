@@ -60,15 +60,16 @@ PB_HD void face_nodes(const Grid& g, long long f, long long& p0, long long& p1) 
 enum { CUTERR_TOO_MANY_CUTS = 1, CUTERR_BAD_CUT_COUNT = 2, CUTERR_CONCAVE = 4, CUTERR_IFACE_NOT_FOUND = 8 };
 
 // detect_node_position (cuthho_geom.hpp:118-130): strict < 0 is the negative side
-__global__ void cut_node_position_kernel(LevelSet L, long long npoints, const double2* __restrict__ pts, int* __restrict__ node_loc) {
-    for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < npoints; p += (long long)gridDim.x * blockDim.x)
+// (all kernels of this file walk an index range [begin, end) of GLOBAL point / face / cell ids: the rows a strip context needs)
+__global__ void cut_node_position_kernel(LevelSet L, long long begin, long long npoints, const double2* __restrict__ pts, int* __restrict__ node_loc) {
+    for (long long p = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; p < npoints; p += (long long)gridDim.x * blockDim.x)
         node_loc[p] = ls_eval(L, pts[p].x, pts[p].y) < 0 ? PB_IN_NEGATIVE_SIDE : PB_IN_POSITIVE_SIDE;
 }
 
 // detect_cut_faces (cuthho_geom.hpp:132-161)
-__global__ void cut_faces_kernel(LevelSet L, Grid g, long long nfaces, const double2* __restrict__ pts, int* __restrict__ face_loc,
+__global__ void cut_faces_kernel(LevelSet L, Grid g, long long begin, long long nfaces, const double2* __restrict__ pts, int* __restrict__ face_loc,
                                  double2* __restrict__ face_ip) {
-    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nfaces; f += (long long)gridDim.x * blockDim.x) {
+    for (long long f = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nfaces; f += (long long)gridDim.x * blockDim.x) {
         long long i0, i1; face_nodes(g, f, i0, i1);
         const double2 a = pts[i0], b = pts[i1];
         const double l0 = ls_eval(L, a.x, a.y), l1 = ls_eval(L, b.x, b.y);
@@ -81,9 +82,10 @@ __global__ void cut_faces_kernel(LevelSet L, Grid g, long long nfaces, const dou
 }
 
 // move_nodes, first loop (cuthho_geom.hpp:466-510): a cut closer than 0.4 |F| to an end node pushes that node away
-__global__ void cut_displacements_kernel(Grid g, long long nfaces, const double2* __restrict__ pts, const int* __restrict__ face_loc,
+// (pbegin, pend): only nodes of this range collect displacements (faces of the halo rows also touch nodes outside it)
+__global__ void cut_displacements_kernel(Grid g, long long begin, long long nfaces, long long pbegin, long long pend, const double2* __restrict__ pts, const int* __restrict__ face_loc,
                                          const double2* __restrict__ face_ip, double* __restrict__ disp_xy, int* __restrict__ displaced) {
-    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nfaces; f += (long long)gridDim.x * blockDim.x) {
+    for (long long f = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nfaces; f += (long long)gridDim.x * blockDim.x) {
         if (face_loc[f] != PB_ON_INTERFACE) continue;
         long long i0, i1; face_nodes(g, f, i0, i1);
         const double2 a = pts[i0], b = pts[i1], ip = face_ip[f];
@@ -94,6 +96,7 @@ __global__ void cut_displacements_kernel(Grid g, long long nfaces, const double2
         if (closeness < thresh) ofs = i0;
         else if (closeness > 1.0 - thresh) ofs = i1;
         else continue;
+        if (ofs < pbegin || ofs >= pend) continue;
         const double dx = __dsub_rn(barx, ip.x) / 2.0, dy = __dsub_rn(bary, ip.y) / 2.0;
         // displacement = displacement - delta; a node receives at most two contributions for a smooth interface, and
         // floating-point addition of two terms is commutative, so the atomic order does not change the bits
@@ -101,18 +104,18 @@ __global__ void cut_displacements_kernel(Grid g, long long nfaces, const double2
         displaced[ofs] = 1;
     }
 }
-__global__ void cut_apply_displacements_kernel(long long npoints, double2* __restrict__ pts, const double* __restrict__ disp_xy, const int* __restrict__ displaced) {
-    for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < npoints; p += (long long)gridDim.x * blockDim.x)
+__global__ void cut_apply_displacements_kernel(long long begin, long long npoints, double2* __restrict__ pts, const double* __restrict__ disp_xy, const int* __restrict__ displaced) {
+    for (long long p = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; p < npoints; p += (long long)gridDim.x * blockDim.x)
         if (displaced[p]) { double2 v = pts[p]; v.x = __dadd_rn(v.x, disp_xy[2 * p]); v.y = __dadd_rn(v.y, disp_xy[2 * p + 1]); pts[p] = v; }
 }
 
 // move_nodes, last loop (cuthho_geom.hpp:520-542): a displaced node must not make a cell concave;
 // detect_cut_cells (cuthho_geom.hpp:275-340): 0 cut faces -> side by the vertices (POSITIVE only if all ls > 0),
 // 2 cut faces -> ON_INTERFACE with the interface oriented so that the left normal points to the negative side.
-__global__ void cut_cells_kernel(LevelSet L, Grid g, long long ncells, const double2* __restrict__ pts, const int* __restrict__ displaced,
+__global__ void cut_cells_kernel(LevelSet L, Grid g, long long begin, long long ncells, const double2* __restrict__ pts, const int* __restrict__ displaced,
                                  const int* __restrict__ face_loc, const double2* __restrict__ face_ip, int* __restrict__ cell_loc,
                                  double2* __restrict__ cell_p01, int* __restrict__ is_cut, int* __restrict__ err) {
-    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x) {
+    for (long long c = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x) {
         const long long ci = c % g.Nx, cj = c / g.Nx, p0 = grid_point(g, ci, cj);
         const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
         double2 v[4];
@@ -149,8 +152,8 @@ __global__ void cut_cells_kernel(LevelSet L, Grid g, long long ncells, const dou
 }
 
 // cut list: slot -> cell from the exclusive scan of is_cut
-__global__ void cut_compact_kernel(long long ncells, const int* __restrict__ is_cut, const int* __restrict__ slot, int* __restrict__ cut_cells) {
-    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x)
+__global__ void cut_compact_kernel(long long begin, long long ncells, const int* __restrict__ is_cut, const int* __restrict__ slot, int* __restrict__ cut_cells) {
+    for (long long c = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncells; c += (long long)gridDim.x * blockDim.x)
         if (is_cut[c]) cut_cells[slot[c]] = (int)c;
 }
 

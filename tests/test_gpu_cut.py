@@ -151,6 +151,43 @@ def test_cut_strip_contexts_assemble_the_same_rows(k, N, cuts):
     whole.close()
 
 
+@pytest.mark.parametrize("N,cuts", [(20, (0, 7, 13, 20)), (33, (0, 5, 17, 18, 33))])
+def test_strip_preprocessing_is_the_window_of_the_whole(N, cuts):
+    """a strip context classifies only the rows it needs (own cell rows + ghost row, their faces and vertices): inside that window
+    its user data and displaced points are the whole-mesh ones bit for bit, outside it PB_UNDEF; owned cut cells add up"""
+    whole = pb.Context(0)
+    gpu_cut_mesh(whole, N, 4)
+    W = whole.cut_download(); Wp = whole.points()
+    wcut = np.flatnonzero(W["cell_loc"] == PB.ON_INTERFACE)
+    owned_total = 0
+    for rb, re in zip(cuts[:-1], cuts[1:]):
+        c = pb.Context(0)
+        c.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT, row_begin=rb, row_end=re)
+        c.cut_levelset(0, 0.35, 0.5, 0.5); c.cut_preprocess(4)
+        D = c.cut_download(); P = c.points()
+        r0 = max(rb - 1, 0)
+        cw = slice(r0 * N, re * N)
+        fw = slice(r0 * (2 * N + 1), (re + 1) * (2 * N + 1) if re < N else whole.nfaces)
+        pw = slice(r0 * (N + 1), min(re + 2, N + 1) * (N + 1))
+        assert np.array_equal(D["cell_loc"][cw], W["cell_loc"][cw]) and np.array_equal(D["face_loc"][fw], W["face_loc"][fw])
+        assert np.array_equal(D["node_loc"][pw], W["node_loc"][pw])
+        cutf = W["face_loc"][fw] == PB.ON_INTERFACE
+        assert np.array_equal(D["face_ip"][fw][cutf], W["face_ip"][fw][cutf])
+        assert np.array_equal(P[pw], Wp[pw])                               # displaced vertices of the window
+        for name, w in (("cell_loc", cw), ("face_loc", fw), ("node_loc", pw)):
+            outside = np.ones(len(D[name]), bool); outside[w] = False
+            assert np.all(D[name][outside] == PB.UNDEF)
+        mine = wcut[(wcut >= cw.start) & (wcut < cw.stop)]
+        held, owned = c.cut_counts_owned()
+        assert held == len(mine) and owned == int((mine >= rb * N).sum())
+        sel = np.searchsorted(wcut, mine)
+        assert np.array_equal(D["iface_pts"], W["iface_pts"][sel])
+        owned_total += owned
+        c.close()
+    assert owned_total == len(wcut)
+    whole.close()
+
+
 def test_config1_anchor_through_the_gpu_path():
     """BASELINE config 1, `cuthho_square -f -M 32 -N 32 -k 1` (mirror of test_oracle_golden.py::test_config1_anchor): 10112
     full-system unknowns = 1024 cells x 6 + 3968 condensed face unknowns, 92 cut cells, 48 displaced nodes, H1 error
