@@ -279,6 +279,26 @@ def interface_record(args, dev, pb, PB):
     return out
 
 
+def bind_to_gpu_numa_node(dev):
+    """Run this process on the CPUs NVML reports as local to GPU `dev`, so that the pinned host buffers allocated afterwards
+    (first touch) sit on that GPU's NUMA node and the per-step copies do not all cross one socket.  Returns a description."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(dev)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus = sorted(cpus & allowed)
+        if cpus and len(cpus) < len(allowed):
+            os.sched_setaffinity(0, cpus)
+            return f"bound to {len(cpus)} CPUs local to GPU {dev} ({cpus[0]}-{cpus[-1]})"
+        return "GPU-local CPU set equals the allowed set: no binding needed"
+    except Exception as e:          # recorded, never fatal
+        return f"not bound ({type(e).__name__}: {str(e)[:80]})"
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -292,6 +312,7 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = local_rank
+    numa = bind_to_gpu_numa_node(dev) if world > 1 else "single rank: not bound"
     k, N = args.k, args.N
     Nx, Ny = N, N * world                      # weak scaling: every rank owns an N x N strip of an N x (N*world) mesh
     hdi = pb.hho_degree_info(k + 1, k)
@@ -300,8 +321,8 @@ def run_ours(args, rank, world, local_rank):
     assert (ctx.row_begin, ctx.row_end) == (rank * N, (rank + 1) * N)
     # FP64 roofline denominator: register-resident DFMA chains, with the SM clock sampled while they run, so that the
     # probe can be checked against 148 SMs x 64 FMA/clk x 2 flop x f_measured
-    with ClockSampler(dev) as pclk:
-        probes = [ctx.probe_fp64_peak() for _ in range(6)]
+    with ClockSampler(dev) as pclk:          # ~1.5 s of back-to-back probes: nvidia-smi samples every 100 ms and must see the clock UNDER this load
+        probes = [ctx.probe_fp64_peak() for _ in range(40)]
     fp64_peak = max(probes)
     pc = pclk.summary()
     nsm = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -451,9 +472,9 @@ def run_ours(args, rank, world, local_rank):
                         "executed_achieved": exec_tf, "executed_frac": exec_tf / fp64_peak if exec_tf is not None else None,
                         "executed_note": "flops K1 actually issues / time / peak = FP64-pipe utilisation (agrees with ncu's sm__pipe_fp64_cycles_active); K1 needs fewer flops than the reference algorithm "
                                          "(stiffness from moments, fancy == naive-operator/diam for HHO(k+1,k))",
-                        "peak_source": "measured on this GPU by pb_probe_fp64_peak (register-resident DFMA chains, best of 6); MEASURED_PEAKS.json has no fp64 entry",
+                        "peak_source": "measured on this GPU by pb_probe_fp64_peak (register-resident DFMA chains, best of 40 back-to-back calls); MEASURED_PEAKS.json has no fp64 entry",
                         "peak_check": {"sm_mhz_during_probe": pc["sm_mhz"], "sms": nsm, "tflops_at_that_clock": peak_check, "probe_over_check": fp64_peak / peak_check if peak_check else None,
-                                       "at_max_clock": nsm * 64 * 2 * (pc["sm_max_mhz"] or 0) * 1e6 / 1e12, "probes": probes},
+                                       "at_max_clock": nsm * 64 * 2 * (pc["sm_max_mhz"] or 0) * 1e6 / 1e12, "probe_min_max": [min(probes), max(probes)], "clock_samples": pc["samples"], "reasons": pc["reasons"]},
                         "flop_per_cell": flop, "executed_flop_per_cell": EXECUTED_FLOP_PER_CELL.get(k), "flop_model": "flop_per_cell: reference-algorithm flops (SURVEY 8d)", "ms_per_launch": k1,
                         "traffic": (ncu_traffic("local_uncut_kernel", N, k) or {}).get("bytes"),
                         "algorithmic_bytes": int(k1_cells * (64 + 8 * (hdi.fbs * 4) * (hdi.fbs * 4 + 1 + hdi.cbs) + 8 * hdi.cbs)),
@@ -462,7 +483,8 @@ def run_ours(args, rank, world, local_rank):
            "e2e": {"value": cells_total / (e2e_ms * 1e-3), "unit": "cells/s", "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                    "ms_per_step": e2e_ms, "rhs_checksum": checksum,
                    "how": "pb_assemble_pipelined: per step, vertices host->device and condensed rhs device->host on copy streams overlapping the kernels of the neighbouring steps",
-                   "serial_ms_per_step": e2e_serial_ms, "serial_value": cells_total / (e2e_serial_ms * 1e-3)},
+                   "serial_ms_per_step": e2e_serial_ms, "serial_value": cells_total / (e2e_serial_ms * 1e-3), "host_numa": numa,
+                   "why_the_rhs": "the step's result on the host is assembler.RHS, which the reference's drivers read after finalize(); the matrix stays on the device for the solve"},
            "gpu_launches": 2 * args.steps, "cg": cg}
     ctx.close()
     if not args.no_cut:

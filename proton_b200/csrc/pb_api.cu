@@ -74,6 +74,7 @@ struct pb_ctx {
     double *ob_alpha = nullptr, *ob_beta = nullptr, *ob_gamma = nullptr, *ob_xprev = nullptr; unsigned char* ob_inA = nullptr; bool ob_ready = false;
     // multi-GPU
     int rank = 0, world = 1; void* comm = nullptr;
+    cudaStream_t s_halo = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;      // halo exchange beside the interior rows of the SpMV
     // timings
     cudaEvent_t ev[4]{};
     double ms_local = 0, ms_scatter = 0, ms_pcg = 0;
@@ -199,6 +200,7 @@ extern "C" pb_status pb_ctx_destroy(pb_ctx* ctx) {
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->ev_in) cudaEventDestroy(ctx->ev_in); if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
     if (ctx->s_in) cudaStreamDestroy(ctx->s_in); if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
+    if (ctx->s_halo) cudaStreamDestroy(ctx->s_halo); if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork); if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx; return PB_OK;
 }

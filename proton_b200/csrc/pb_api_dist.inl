@@ -79,8 +79,9 @@ extern "C" pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsign
 // ---- halo exchange of a face vector stored for the columns [col_lo, col_hi): `full` points at col_lo, the owned part
 // starts `down` doubles in and has n entries.  Rank r-1 needs my first face-row part (its upper halo: the faces
 // through h(., row_begin)), rank r+1 needs my last face row (its lower halo).
-static pb_status halo_exchange(pb_ctx* ctx, double* full) {
+static pb_status halo_exchange(pb_ctx* ctx, double* full, cudaStream_t stream = nullptr) {
     if (ctx->world == 1) return PB_OK;
+    if (!stream) stream = ctx->stream;
     const Grid& g = ctx->grid; const Strip& s = ctx->strip; const int F = ctx->F;
     const long long n = ctx->nrows, down = (s.cf_begin - s.col_lo) * F, up = (s.col_hi - s.cf_end) * F;
     const long long nfree = num_free_faces(g);
@@ -90,12 +91,12 @@ static pb_status halo_exchange(pb_ctx* ctx, double* full) {
     double* own = full + down;
     NCK(nccl_dl::g.GroupStart());
     if (ctx->rank > 0) {
-        NCK(nccl_dl::g.Send(own, (size_t)to_prev, nccl_dl::Float64, ctx->rank - 1, ctx->comm, ctx->stream));
-        NCK(nccl_dl::g.Recv(full, (size_t)down, nccl_dl::Float64, ctx->rank - 1, ctx->comm, ctx->stream));
+        NCK(nccl_dl::g.Send(own, (size_t)to_prev, nccl_dl::Float64, ctx->rank - 1, ctx->comm, stream));
+        NCK(nccl_dl::g.Recv(full, (size_t)down, nccl_dl::Float64, ctx->rank - 1, ctx->comm, stream));
     }
     if (ctx->rank < ctx->world - 1) {
-        NCK(nccl_dl::g.Send(own + n - to_next, (size_t)to_next, nccl_dl::Float64, ctx->rank + 1, ctx->comm, ctx->stream));
-        NCK(nccl_dl::g.Recv(own + n, (size_t)up, nccl_dl::Float64, ctx->rank + 1, ctx->comm, ctx->stream));
+        NCK(nccl_dl::g.Send(own + n - to_next, (size_t)to_next, nccl_dl::Float64, ctx->rank + 1, ctx->comm, stream));
+        NCK(nccl_dl::g.Recv(own + n, (size_t)up, nccl_dl::Float64, ctx->rank + 1, ctx->comm, stream));
     }
     NCK(nccl_dl::g.GroupEnd());
     return PB_OK;
@@ -121,7 +122,7 @@ static pb_status ensure_solver(pb_ctx* ctx) {
         free_solver(ctx);
         CK(dalloc(ctx, &ctx->x, (size_t)n)); CK(dalloc(ctx, &ctx->r, (size_t)n)); CK(dalloc(ctx, &ctx->z, (size_t)n));
         CK(dalloc(ctx, &ctx->dfull, (size_t)nfull)); CK(dalloc(ctx, &ctx->y, (size_t)n)); CK(dalloc(ctx, &ctx->iA, (size_t)n));
-        CK(dalloc(ctx, &ctx->parts, (size_t)4 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));
+        CK(dalloc(ctx, &ctx->parts, (size_t)6 * PCG_MAX_BLOCKS)); CK(dalloc(ctx, &ctx->scal, 4));      // [d.y: 2 | r.r | r.z | scratch of the multigrid: 2] x PCG_MAX_BLOCKS
         CK(cudaMemsetAsync(ctx->dfull, 0, (size_t)nfull * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->x, 0, (size_t)n * 8, ctx->stream));
         ctx->solver_n = n; ctx->solver_nfull = nfull;
@@ -138,7 +139,10 @@ static pb_status ensure_block_inverse(pb_ctx* ctx) {
 // ---- y = A v on the owned rows (v with halos), with the partial sums of v.y: which kernel, which grid
 struct SpmvPlan {
     long long n, xoff, down; int F, lpr, nblk, nblk_sp, nblk_irr; bool use_csr;
-    int ndy() const { return nblk_sp + nblk_irr; }      // number of d.y partials
+    // several ranks: the block rows [0, lo_rows) (first face row of the strip) and [nbr - hi_rows, nbr) (last face row) are the only
+    // ones that read halo columns; the interior is launched while the halo travels (nblk_bnd blocks for each boundary launch)
+    bool overlap = false; long long lo_rows = 0, hi_rows = 0; int nblk_lo = 0, nblk_hi = 0;
+    int ndy() const { return nblk_sp + nblk_irr + nblk_lo + nblk_hi; }      // number of d.y partials
 };
 static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
     SpmvPlan P{};
@@ -157,11 +161,56 @@ static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
         const int occ = F == 1 ? spmv_blk_blocks_per_sm<1>() : F == 2 ? spmv_blk_blocks_per_sm<2>() : F == 3 ? spmv_blk_blocks_per_sm<3>() : spmv_blk_blocks_per_sm<4>();
         P.nblk_sp = nsm * occ; if (P.nblk_sp > PCG_MAX_BLOCKS) P.nblk_sp = PCG_MAX_BLOCKS;
         const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < P.nblk_sp) P.nblk_sp = (int)(wantg < 1 ? 1 : wantg);
+        if (ctx->world > 1 && ctx->comm && !ctx->general_csr && !getenv("PB_NO_HALO_OVERLAP")) {
+            const Grid& g = ctx->grid; const long long nbr = n / F, per = 2 * g.Nx - 1;
+            const long long lo = ctx->rank > 0 ? std::min(per, nbr) : 0;
+            const long long hi = ctx->rank < ctx->world - 1 ? ctx->strip.cf_end - compress_row_start(g, g.row_end - 1) : 0;
+            if (lo + hi > 0 && nbr - lo - hi >= 4 * per) {      // enough interior rows to hide the exchange behind
+                P.overlap = true; P.lo_rows = lo; P.hi_rows = hi;
+                auto blocks_for = [](long long rows) { return rows ? (int)std::max<long long>(1, std::min<long long>(PCG_MAX_BLOCKS / 8, (rows * 8 + PCG_THREADS - 1) / PCG_THREADS)) : 0; };
+                P.nblk_lo = blocks_for(lo); P.nblk_hi = blocks_for(hi);
+                const long long wanti = ((nbr - lo - hi) * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wanti < P.nblk_sp) P.nblk_sp = (int)(wanti < 1 ? 1 : wanti);
+            }
+        }
     }
     return P;
 }
+// block SpMV on the block rows [r0, r0 + cnt) of the owned rows, partial sums of v.y into `parts` (one per block)
+static void launch_spmv_blk_range(pb_ctx* ctx, const SpmvPlan& P, long long r0, long long cnt, int blocks, const double* vfull, double* y, double* parts) {
+    const int F = P.F; cudaStream_t sm = ctx->stream;
+#define PB_SPMV_R(F_) pcg_spmv_blk_kernel<8, F_, 0><<<blocks, PCG_THREADS, 0, sm>>>(cnt * F, P.xoff, ctx->brows + r0, ctx->brp + r0, ctx->val, vfull, P.down + r0 * F, y + r0 * F, parts, ctx->cg)
+    switch (F) { case 1: PB_SPMV_R(1); break; case 2: PB_SPMV_R(2); break; case 3: PB_SPMV_R(3); break; default: PB_SPMV_R(4); break; }
+#undef PB_SPMV_R
+}
+// halo exchange of vfull + y = A v.  Several ranks: the exchange runs on its own stream beside the interior block rows, the rows of
+// the strip's first and last face row follow once the halo has arrived (fork / join by events, also valid inside a graph capture).
+static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull, double* y, double* p_dy);
+static pb_status spmv_with_halo(pb_ctx* ctx, const SpmvPlan& P, double* vfull, double* y, double* p_dy) {
+    if (!P.overlap) {
+        pb_status st = halo_exchange(ctx, vfull); if (st != PB_OK) return st;
+        return launch_spmv(ctx, P, vfull, y, p_dy);
+    }
+    if (!ctx->s_halo) {
+        CK(cudaStreamCreateWithFlags(&ctx->s_halo, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    }
+    const long long nbr = P.n / P.F;
+    CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->s_halo, ctx->ev_fork, 0));
+    { pb_status st = halo_exchange(ctx, vfull, ctx->s_halo); if (st != PB_OK) return st; }
+    CK(cudaEventRecord(ctx->ev_join, ctx->s_halo));
+    launch_spmv_blk_range(ctx, P, P.lo_rows, nbr - P.lo_rows - P.hi_rows, P.nblk_sp, vfull, y, p_dy);
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    if (P.lo_rows) launch_spmv_blk_range(ctx, P, 0, P.lo_rows, P.nblk_lo, vfull, y, p_dy + P.nblk_sp + P.nblk_irr);
+    if (P.hi_rows) launch_spmv_blk_range(ctx, P, nbr - P.hi_rows, P.hi_rows, P.nblk_hi, vfull, y, p_dy + P.nblk_sp + P.nblk_irr + P.nblk_lo);
+    CK(cudaGetLastError());
+    return PB_OK;
+}
 static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull, double* y, double* p_dy) {
     cudaStream_t sm = ctx->stream; const long long n = P.n; const int F = P.F;
+    if (P.overlap) { launch_spmv_blk_range(ctx, P, 0, n / F, P.nblk_sp, vfull, y, p_dy);      // (callers that exchanged the halo themselves)
+        if (P.nblk_lo + P.nblk_hi) cudaMemsetAsync(p_dy + P.nblk_sp + P.nblk_irr, 0, (size_t)(P.nblk_lo + P.nblk_hi) * 8, sm);
+        CK(cudaGetLastError()); return PB_OK; }
 #define PB_SPMV(LPR_, F_, CS_) pcg_spmv_blk_kernel<LPR_, F_, CS_><<<P.nblk_sp, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->brows, ctx->brp, ctx->val, vfull, P.down, y, p_dy, ctx->cg)
     if (P.use_csr) {
         switch (P.lpr) {
@@ -229,10 +278,9 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     CK(cudaGetLastError());
     // one iteration = [dir, commit] (skipped in the very first one), halo exchange, spmv, xrz (+ all-reduces)
     auto spmv_xrz = [&]() -> pb_status {
-        { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
-        { pb_status st = launch_spmv(ctx, plan, ctx->dfull, ctx->y, p_dy); if (st != PB_OK) return st; }
+        { pb_status st = spmv_with_halo(ctx, plan, ctx->dfull, ctx->y, p_dy); if (st != PB_OK) return st; }
         if (multi) {
-            pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(nblk_sp, p_dy, s_dy, nullptr, nullptr);
+            pcg_sum_partials_kernel<<<1, PCG_THREADS, 0, sm>>>(plan.ndy(), p_dy, s_dy, nullptr, nullptr);
             NCK(nccl_dl::g.AllReduce(s_dy, s_dy, 1, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, sm));
         }
         if (blockpre) {

@@ -131,8 +131,7 @@ static pb_status mg_setup(pb_ctx* ctx) {
     const int iters = 14;
     for (int it = 0; it <= iters; it++) {
         if (it > 0) {
-            { pb_status st = halo_exchange(ctx, M.wfull); if (st != PB_OK) return st; }
-            { pb_status st = launch_spmv(ctx, plan, M.wfull, ctx->y, parts + PCG_MAX_BLOCKS); if (st != PB_OK) return st; }
+            { pb_status st = spmv_with_halo(ctx, plan, M.wfull, ctx->y, parts + 4 * PCG_MAX_BLOCKS); if (st != PB_OK) return st; }
 #define PB_PW(F_) mg_pow_apply_kernel<F_><<<plan.nblk, PCG_THREADS, 0, sm>>>(nbr, ctx->iAb, ctx->y, w, parts)
             PB_MG_F(PB_PW);
 #undef PB_PW
@@ -192,7 +191,7 @@ static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan, const double* r, in
     MgState& M = ctx->mg; cudaStream_t sm = ctx->stream;
     const int F = ctx->F; const long long n = ctx->nrows, nbr = n / F, down = plan.down;
     double *z = M.zfull + down, *w = M.wfull + down, *rs = M.resfull + down;
-    double* pdummy = ctx->parts + PCG_MAX_BLOCKS;      // the SpMV's v.y partials are not used here
+    double* pdummy = ctx->parts + 4 * PCG_MAX_BLOCKS;      // the SpMV's v.y partials are not used here (scratch area of the partials buffer)
     const double lmax = M.lmax, lmin = MG_CHEB_LO * lmax, theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
     const MgCut C = mg_cut_of(ctx);
     auto cheb = [&](int first, int have_y, int acc, int last, double c1, double c2) {
@@ -200,10 +199,7 @@ static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan, const double* r, in
         PB_MG_F(PB_CH);
 #undef PB_CH
     };
-    auto spmv = [&](double* vfull) -> pb_status {
-        pb_status st = halo_exchange(ctx, vfull); if (st != PB_OK) return st;
-        return launch_spmv(ctx, plan, vfull, ctx->y, pdummy);
-    };
+    auto spmv = [&](double* vfull) -> pb_status { return spmv_with_halo(ctx, plan, vfull, ctx->y, pdummy); };
     auto steps = [&](bool from_zero) -> pb_status {      // the Chebyshev recurrence after its first step
         double rho = 1.0 / sigma;
         for (int k = 1; k < nu; k++) {
@@ -284,8 +280,7 @@ static pb_status pcg_multigrid(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result*
             pcg_dir_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_n, c_rr, c_rz, z, ctx->d, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg);
             pcg_commit_kernel<<<1, PCG_THREADS, 0, sm>>>(c_n, c_rr, c_rz, p->convergence_threshold, p->divergence_threshold, p->max_iter, ctx->cg, ctx->hist, ctx->hist_cap);
         }
-        { pb_status st = halo_exchange(ctx, ctx->dfull); if (st != PB_OK) return st; }
-        { pb_status st = launch_spmv(ctx, plan, ctx->dfull, ctx->y, p_dy); if (st != PB_OK) return st; }
+        { pb_status st = spmv_with_halo(ctx, plan, ctx->dfull, ctx->y, p_dy); if (st != PB_OK) return st; }
         { pb_status st = reduce1(plan.ndy(), p_dy, s_dy); if (st != PB_OK) return st; }
         mg_xr_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, c_ndy, c_dy, ctx->d, ctx->y, ctx->x, ctx->r, p_rr, ctx->cg);
         { pb_status st = reduce1(nblk, p_rr, s_rr); if (st != PB_OK) return st; }

@@ -8,7 +8,7 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 k = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 ctx = pb.Context(0)
 ctx.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT)
-ctx.cut_levelset(0, 1.0 / 3.0, 0.5, 0.5)
+ctx.cut_levelset(0, 0.35, 0.5, 0.5)
 ctx.cut_preprocess(4)
 hdi = pb.hho_degree_info(k + 1, k)
 for i in range(4):

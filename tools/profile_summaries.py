@@ -24,7 +24,7 @@ if os.path.exists(src):
         a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += ms
     tot = sum(a[1] for a in agg.values())
     with open(os.path.join(pr, f"{tag}_launches_summary.txt"), "w") as f:
-        f.write(f"# {tag} launch list summary: python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-cg-tol --no-interface (ncu --metrics gpu__time_duration.sum --clock-control none, first 900 launches)\n")
+        f.write(f"# {tag} launch list summary: python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-cg-tol --no-interface (ncu --metrics gpu__time_duration.sum --clock-control none, first launches of the timed program)\n")
         f.write("# kernel, launches, total ms, us/launch, share\n")
         for name, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
             f.write(f"{name:100s} {n:5d} {ms:10.3f} ms {1e3 * ms / n:10.1f} us/launch {100 * ms / tot:5.1f}%\n")
