@@ -232,6 +232,40 @@ def cut_record(args, rank, world, dev, dist, torch, pb, PB, fp64_peak):
                          "flop_model": "reference-algorithm flops (SURVEY 8d; BASELINE.md 4), not executed flops"}}
 
 
+def dist_check_record(rank, world, dev, dist, torch, pb, PB):
+    """N > 1 only: the ranks' joint solution against a one-GPU solve of the same system, inside the driver-run bench (the
+    standalone version is tests/dist_gpu_check.py).  cutHHO fictitious-domain k=2 on 256x256, multigrid-PCG to 1e-13: face
+    solution to 1e-8 relative (global norm), the driver's H1 error summed over the ranks to 1e-8, same iteration count +-2."""
+    import numpy as np
+    from proton_b200.dist import make_rank_context
+    N, k = 256, 2
+    mip = pb.mesh_init_params(N, N); hdi = pb.hho_degree_info(k + 1, k)
+
+    def solve(ctx):
+        ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)
+        return ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 5000, 3))
+    ctx = make_rank_context(mip, PB.QUAD_POLY_DUNAVANT, rank, world, dev, dist)
+    r = solve(ctx)
+    faces = ctx.face_solution()
+    h1 = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(h1)
+    L = pb.strip_layout(N, N, ctx.row_begin, ctx.row_end, hdi.fbs)
+    ctx.close()
+    ref = pb.Context(dev)                      # every rank repeats the small one-GPU solve (no gather of the solution needed)
+    ref.mesh(mip, PB.QUAD_POLY_DUNAVANT)
+    r1 = solve(ref)
+    x1 = ref.face_solution(); e1 = float(ref.error_norms()[0])
+    ref.close()
+    mine = x1[L["cf_begin"] * hdi.fbs: L["cf_begin"] * hdi.fbs + L["n_rows"]]
+    t = torch.tensor([float(np.sum((faces - mine) ** 2)), float(np.sum(mine ** 2))], dtype=torch.float64, device=f"cuda:{dev}"); dist.all_reduce(t)
+    rel = float(t[0]) ** 0.5 / float(t[1]) ** 0.5
+    h1_rel = abs(float(h1[0]) - e1) / e1
+    ok = (r["exit_reason"] == PB.CG_CONVERGED and r1["exit_reason"] == PB.CG_CONVERGED and rel < 1e-8 and h1_rel < 1e-8 and abs(r["iterations"] - r1["iterations"]) <= 2)
+    return {"workload": f"cutHHO fictitious-domain k=2, {N}x{N}, {world} ranks against one GPU, multigrid-PCG to 1e-13", "passed": bool(ok),
+            "solution_rel_diff": rel, "h1_error_sq": float(h1[0]), "h1_error_sq_one_gpu": e1, "h1_rel_diff": h1_rel,
+            "iterations": r["iterations"], "iterations_one_gpu": r1["iterations"]}
+
+
 def obstacle_record(args, dev, pb, PB):
     """BASELINE config 5 (single GPU): HHO obstacle problem, face degree 1, ob_N x ob_N quads on [-1,1]^2, the driver's active-set
     loop (obstacle.cpp:119-198, capped at 50 outer iterations like the reference)."""
@@ -491,6 +525,9 @@ def run_ours(args, rank, world, local_rank):
         out["target_cut"] = cut_record(args, rank, world, dev, dist, torch, pb, PB, fp64_peak)
     if world == 1 and not args.no_obstacle:
         out["obstacle"] = obstacle_record(args, dev, pb, PB)
+    if world > 1:
+        out["dist_check"] = dist_check_record(rank, world, dev, dist, torch, pb, PB)
+        assert out["dist_check"]["passed"], f"multi-GPU solution differs from the one-GPU solve: {out['dist_check']}"
     if world == 1 and not args.no_interface:
         out["interface"] = interface_record(args, dev, pb, PB)
     if rank == 0:

@@ -22,7 +22,7 @@ class PB:
     FUN_SINSIN, FUN_OBSTACLE, FUN_TANH = 0, 1, 2
     IN_NEGATIVE_SIDE, IN_POSITIVE_SIDE, ON_INTERFACE, UNDEF = 0, 1, 2, 3
     CG_CONVERGED, CG_DIVERGED, CG_MAX_ITER_REACHED = 0, 1, 2
-    LOCAL_LC, LOCAL_OPER, LOCAL_RHS, LOCAL_SCHUR, LOCAL_SCHUR_RHS, LOCAL_REC_A, LOCAL_REC_B = range(7)
+    LOCAL_LC, LOCAL_OPER, LOCAL_RHS, LOCAL_SCHUR, LOCAL_SCHUR_RHS, LOCAL_REC_A, LOCAL_REC_B, LOCAL_DATA = range(8)
 
 
 class _AssemblyParams(C.Structure):
@@ -265,7 +265,7 @@ class Context:
         count = self.ncells_local - cell_begin if count is None else count
         h = self.hdi; nf = 4 * h.fbs; n = h.cbs + nf
         shape = {PB.LOCAL_LC: (n, n), PB.LOCAL_OPER: (n, h.rbs), PB.LOCAL_RHS: (h.cbs,), PB.LOCAL_SCHUR: (nf, nf), PB.LOCAL_SCHUR_RHS: (nf,),
-                 PB.LOCAL_REC_A: (nf, h.cbs), PB.LOCAL_REC_B: (h.cbs,)}[what]
+                 PB.LOCAL_REC_A: (nf, h.cbs), PB.LOCAL_REC_B: (h.cbs,), PB.LOCAL_DATA: (n, n)}[what]
         out = np.zeros((count,) + shape)
         self._ck(lib().pb_get_local(self._h, what, cell_begin, count, _ptr(out)))
         # device layout is column-major: out[c, col, row]; return [c, row, col]

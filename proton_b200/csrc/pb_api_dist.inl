@@ -161,7 +161,9 @@ static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
         const int occ = F == 1 ? spmv_blk_blocks_per_sm<1>() : F == 2 ? spmv_blk_blocks_per_sm<2>() : F == 3 ? spmv_blk_blocks_per_sm<3>() : spmv_blk_blocks_per_sm<4>();
         P.nblk_sp = nsm * occ; if (P.nblk_sp > PCG_MAX_BLOCKS) P.nblk_sp = PCG_MAX_BLOCKS;
         const long long wantg = (n / F * 8 + PCG_THREADS - 1) / PCG_THREADS; if (wantg < P.nblk_sp) P.nblk_sp = (int)(wantg < 1 ? 1 : wantg);
-        if (ctx->world > 1 && ctx->comm && !ctx->general_csr && !getenv("PB_NO_HALO_OVERLAP")) {
+        // opt-in (PB_HALO_OVERLAP=1): measured on 2 GPUs at 4096^2 the two extra boundary launches and the fork / join cost what the hidden
+        // exchange (98 KB, ~25 us) saves: Jacobi-PCG 3.007 against 2.970 ms per iteration, multigrid-PCG 10.19 against 10.11 (profiles/r2m_overlap.txt)
+        if (ctx->world > 1 && ctx->comm && !ctx->general_csr && getenv("PB_HALO_OVERLAP")) {
             const Grid& g = ctx->grid; const long long nbr = n / F, per = 2 * g.Nx - 1;
             const long long lo = ctx->rank > 0 ? std::min(per, nbr) : 0;
             const long long hi = ctx->rank < ctx->world - 1 ? ctx->strip.cf_end - compress_row_start(g, g.row_end - 1) : 0;
