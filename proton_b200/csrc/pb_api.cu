@@ -288,9 +288,9 @@ static pb_status scatter_system(pb_ctx* ctx);
 #include "pb_api_interface.inl"
 
 // ------------------------------------------------------------------------------------------------ stage 1+2
-template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB>
+template <int CD, int FD, int QK, int SK, int RQD, int GS, int TPB, int MINB, int MQ = QK>
 static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A_) {
-    constexpr int QC = cell_qps(QK, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
+    constexpr int QC = cell_qps(MQ, 2 * (FD + 1)), QR = cell_qps(QK, RQD), QCMAX = QC > QR ? QC : QR;
     using SM = LocalSmem<CD, FD, GS, QCMAX>;
     LocalArgs A = A_;
     if (A.ncells >= (1ll << 31)) return cudaErrorInvalidValue;      // K1 indexes local cells with 32 bits
@@ -307,8 +307,8 @@ static cudaError_t launch_local(pb_ctx* c, const LocalArgs& A_) {
         }
         A.stiff = c->stiff_tab;
     }
-    const size_t smem = local_ref_bytes<CD, FD, QK, RQD>() + sizeof(SM) * (TPB / GS);
-    auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS, TPB, MINB>;
+    const size_t smem = local_ref_bytes<CD, FD, QK, RQD, MQ>() + sizeof(SM) * (TPB / GS);
+    auto kern = local_uncut_kernel<CD, FD, QK, SK, RQD, GS, TPB, MINB, MQ>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int bps = 0, nsm = 0;
@@ -352,7 +352,10 @@ static cudaError_t dispatch_local(pb_ctx* c, const LocalArgs& A, int cd, int fd,
     PB_CASE(2, 1, 0, 1, 4, 4, 32, 12) PB_CASE(2, 1, 0, 0, 4, 4, 32, 12)
     PB_CASE(3, 2, 0, 1, 6, 8, 32, 8) PB_CASE(3, 2, 0, 0, 6, 8, 32, 8)
     PB_CASE(4, 3, 0, 1, 8, 16, 32, 5) PB_CASE(4, 3, 0, 0, 8, 16, 32, 5)
-    // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive
+    // HHO(k+1,k), Dunavant fan (uncut cells of cuthho_square): naive.  (Tried in round 2: moments from the 16 tensor Gauss points, which are
+    // exact for them, and the fan only for the load of the cells inside the domain — template parameter MQ of local_uncut_kernel.  Same
+    // matrices to rounding, all tests green, but SLOWER: 73.1 against 63.4 ms at 4096^2, k = 2 (profiles/r2p_fan_moments.txt): the second
+    // quadrature loop lengthens an instruction stream that is already the bottleneck.  The instances are not built.)
     PB_CASE(1, 0, 1, 0, 2, 4, 32, 16)
     PB_CASE(2, 1, 1, 0, 4, 4, 32, 12)
     PB_CASE(3, 2, 1, 0, 6, 8, 32, 8)
