@@ -140,3 +140,16 @@ def test_workspace_follows_the_system_size():
         sizes.append(ctx.n_rows)
     assert sizes[1] > sizes[0]
     ctx.close()
+
+
+@pytest.mark.parametrize("Nx,Ny", [(2, 2), (2, 3), (3, 2), (2, 9), (5, 3)])
+@pytest.mark.parametrize("k", [0, 2])
+def test_tiny_meshes(Nx, Ny, k):
+    """degenerate hierarchies: a single level, one interior vertex, one coarsening direction"""
+    ctx = pb.Context(0)
+    ctx.mesh(pb.mesh_init_params(Nx, Ny)).assemble(pb.hho_degree_info(k + 1, k), fun=PB.FUN_TANH)
+    rj = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 10000, True)); xj = ctx.face_solution()
+    rm = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 10000, 3)); xm = ctx.face_solution()
+    assert rj["exit_reason"] == PB.CG_CONVERGED and rm["exit_reason"] == PB.CG_CONVERGED
+    assert np.linalg.norm(xm - xj) < 1e-8 * np.linalg.norm(xj)
+    ctx.close()
