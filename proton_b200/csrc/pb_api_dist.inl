@@ -142,6 +142,7 @@ struct SpmvPlan {
     // several ranks: the block rows [0, lo_rows) (first face row of the strip) and [nbr - hi_rows, nbr) (last face row) are the only
     // ones that read halo columns; the interior is launched while the halo travels (nblk_bnd blocks for each boundary launch)
     bool overlap = false; long long lo_rows = 0, hi_rows = 0; int nblk_lo = 0, nblk_hi = 0;
+    const float* valf = nullptr;      // set by the multigrid preconditioner: run the block product on the single-precision copy of the values
     int ndy() const { return nblk_sp + nblk_irr + nblk_lo + nblk_hi; }      // number of d.y partials
 };
 static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
@@ -180,7 +181,8 @@ static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
 // block SpMV on the block rows [r0, r0 + cnt) of the owned rows, partial sums of v.y into `parts` (one per block)
 static void launch_spmv_blk_range(pb_ctx* ctx, const SpmvPlan& P, long long r0, long long cnt, int blocks, const double* vfull, double* y, double* parts) {
     const int F = P.F; cudaStream_t sm = ctx->stream;
-#define PB_SPMV_R(F_) pcg_spmv_blk_kernel<8, F_, 0><<<blocks, PCG_THREADS, 0, sm>>>(cnt * F, P.xoff, ctx->brows + r0, ctx->brp + r0, ctx->val, vfull, P.down + r0 * F, y + r0 * F, parts, ctx->cg)
+#define PB_SPMV_R(F_) do { if (P.valf) pcg_spmv_blk_kernel<8, F_, 0, float><<<blocks, PCG_THREADS, 0, sm>>>(cnt * F, P.xoff, ctx->brows + r0, ctx->brp + r0, P.valf, vfull, P.down + r0 * F, y + r0 * F, parts, ctx->cg); \
+    else pcg_spmv_blk_kernel<8, F_, 0><<<blocks, PCG_THREADS, 0, sm>>>(cnt * F, P.xoff, ctx->brows + r0, ctx->brp + r0, ctx->val, vfull, P.down + r0 * F, y + r0 * F, parts, ctx->cg); } while (0)
     switch (F) { case 1: PB_SPMV_R(1); break; case 2: PB_SPMV_R(2); break; case 3: PB_SPMV_R(3); break; default: PB_SPMV_R(4); break; }
 #undef PB_SPMV_R
 }
@@ -220,6 +222,8 @@ static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull
         case 8: pcg_spmv_kernel<8><<<P.nblk, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->rowptr, ctx->col, ctx->val, vfull, P.down, y, p_dy, ctx->cg); break;
         default: pcg_spmv_kernel<16><<<P.nblk, PCG_THREADS, 0, sm>>>(n, P.xoff, ctx->rowptr, ctx->col, ctx->val, vfull, P.down, y, p_dy, ctx->cg); break;
         }
+    } else if (P.valf) {
+        launch_spmv_blk_range(ctx, P, 0, n / F, P.nblk_sp, vfull, y, p_dy);
     } else {
         switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
     }

@@ -8,7 +8,7 @@ static void mg_free(pb_ctx* c) {
         MgLevelData& D = M.lev[l];
         dfree(&D.E); dfree(&D.st); dfree(&D.idiag); dfree(&D.x); dfree(&D.b); dfree(&D.r); dfree(&D.t);
     }
-    dfree(&M.resfull); dfree(&M.zfull); dfree(&M.wfull); dfree(&M.lam);
+    dfree(&M.resfull); dfree(&M.zfull); dfree(&M.wfull); dfree(&M.lam); dfree(&M.valf); M.valf_n = 0;
     M.ready = false; M.gen = -1; M.nlev = 0; M.nfull = 0; M.key[0] = M.key[1] = M.key[2] = M.key[3] = 0;
 }
 
@@ -149,6 +149,15 @@ static pb_status mg_setup(pb_ctx* ctx) {
     CK(cudaStreamSynchronize(sm));
     NEED(lam > 0.0 && std::isfinite(lam), PB_ERR_STATE, "pb_pcg: power iteration for the smoother failed (singular diagonal block?)");
     M.lmax = 1.1 * lam;      // the iteration approaches lmax from below
+    // single-precision copy of the values for the SpMVs INSIDE the V-cycle (4 of the 5 products of an iteration): a V-cycle on a
+    // slightly perturbed symmetric matrix is still a fixed SPD operator, so the CG recurrence, which keeps the double matrix, double
+    // vectors and double dot products, converges to the same solution in the same number of iterations, at half the matrix traffic
+    // of those products.  PB_MG_FP64=1 keeps the V-cycle on the double values (the tests compare that variant with the restatement).
+    if (!plan.use_csr && !getenv("PB_MG_FP64")) {
+        if (M.valf_n != ctx->nnz) { CK(dalloc(ctx, &M.valf, (size_t)ctx->nnz)); M.valf_n = ctx->nnz; }
+        mg_val_to_float_kernel<<<148 * 8, 256, 0, sm>>>(ctx->nnz, ctx->val, M.valf);
+        CK(cudaGetLastError());
+    } else { dfree(&M.valf); M.valf_n = 0; }
     CK(cudaMemsetAsync(M.wfull, 0, (size_t)M.nfull * 8, sm)); CK(cudaMemsetAsync(M.resfull, 0, (size_t)M.nfull * 8, sm));
     M.ready = true; M.gen = ctx->asm_gen;
     return PB_OK;
@@ -187,8 +196,9 @@ static pb_status mg_vcycle_nodes(pb_ctx* ctx) {
 
 // z = M^{-1} r: nu Chebyshev steps, coarse correction through the vertex levels, nu Chebyshev steps (symmetric).
 // r = owned rows; the result is the owned part of mg.zfull.
-static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan, const double* r, int nu) {
+static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan_d, const double* r, int nu) {
     MgState& M = ctx->mg; cudaStream_t sm = ctx->stream;
+    SpmvPlan plan = plan_d; plan.valf = M.valf;      // the products of the V-cycle run on the single-precision copy when there is one
     const int F = ctx->F; const long long n = ctx->nrows, nbr = n / F, down = plan.down;
     double *z = M.zfull + down, *w = M.wfull + down, *rs = M.resfull + down;
     double* pdummy = ctx->parts + 4 * PCG_MAX_BLOCKS;      // the SpMV's v.y partials are not used here (scratch area of the partials buffer)

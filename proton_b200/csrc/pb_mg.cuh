@@ -357,6 +357,11 @@ __global__ void mg_pow_init_kernel(long long n, long long row0, double* __restri
     }
 }
 
+// single-precision copy of the CSR values for the SpMVs of the V-cycle
+__global__ void mg_val_to_float_kernel(long long nnz, const double* __restrict__ val, float* __restrict__ valf) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nnz; i += (long long)gridDim.x * blockDim.x) valf[i] = (float)val[i];
+}
+
 // ------------------------------------------------------------------------------------------------ PCG pieces
 // x += alpha d, r -= alpha y with alpha = rho / (d.y); partial sums of r.r           (solver_cg.hpp:106-110)
 __global__ void mg_xr_kernel(long long n, int nparts, const double* __restrict__ parts_dy, const double* __restrict__ d, const double* __restrict__ y,
@@ -416,6 +421,7 @@ struct MgState {
     MgLevelData lev[MG_MAX_LEVELS]{};
     double lmax = 0.0; double *resfull = nullptr, *zfull = nullptr, *wfull = nullptr, *lam = nullptr;
     long long nfull = 0;
+    float* valf = nullptr; long long valf_n = 0;      // fp32 copy of the CSR values (V-cycle SpMVs), or nullptr
 };
 }  // namespace pb
 #endif

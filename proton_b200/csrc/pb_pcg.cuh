@@ -120,9 +120,11 @@ __global__ void __launch_bounds__(PCG_THREADS, 8) pcg_spmv_kernel(long long n, l
 // array is the scalar CSR one (rows of a face are contiguous).  CS = 1 streams the values with evict-first loads;
 // measured slower (a 504-byte block row is consumed by one lane group over several instructions and needs L1 to merge
 // the partially used sectors), so CS = 0 is what runs.
-template <int LPR, int F, int CS>
+// VT = float: the same product on a single-precision COPY of the values (vectors and accumulation stay double): half the matrix
+// bytes.  Only the multigrid preconditioner uses it (pb_api_mg.inl); the A d of the CG recurrence always runs on the double values.
+template <int LPR, int F, int CS, typename VT = double>
 __global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow* __restrict__ rows, const long long* __restrict__ brp,
-                                    const double* __restrict__ val, const double* __restrict__ dvec, long long down,
+                                    const VT* __restrict__ val, const double* __restrict__ dvec, long long down,
                                     double* __restrict__ y, double* __restrict__ parts_dy, const CgState* st) {
     // one group of LPR lanes per BLOCK row: a lane gathers the vector entry of its columns once and feeds the F scalar
     // rows of the face with it (F x fewer gathers, F independent value loads in flight per column)
@@ -141,7 +143,7 @@ __global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow*
         if (br < nbr) {
             const BlockRow* R = rows + br;
             const int len = R->nb * F;
-            const double* v = val + brp[br] * (F * F);
+            const VT* v = val + brp[br] * (F * F);
 #pragma unroll
             for (int t = 0; t < (7 * F + LPR - 1) / LPR; t++) {
                 const int k = sub + t * LPR;
@@ -149,7 +151,7 @@ __global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow*
                     const int b = k / F, bc = k - b * F;
                     const double xv = dvec[(long long)R->bcol[b] * F + bc - xoff];
 #pragma unroll
-                    for (int a = 0; a < F; a++) acc[a] += (CS ? __ldcs(v + a * len + k) : v[a * len + k]) * xv;
+                    for (int a = 0; a < F; a++) acc[a] += (double)(CS ? __ldcs(v + a * len + k) : v[a * len + k]) * xv;
                 }
             }
         }

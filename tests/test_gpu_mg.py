@@ -30,7 +30,14 @@ def gpu_system(Nx, Ny, k, cut, fun=PB.FUN_SINSIN):
 
 
 @pytest.mark.parametrize("Nx,Ny,k,cut", [(12, 9, 1, False), (8, 8, 2, False), (7, 10, 0, False), (9, 9, 3, False), (12, 12, 1, True), (16, 16, 2, True)])
-def test_hierarchy_and_apply_match_restatement(Nx, Ny, k, cut):
+@pytest.mark.parametrize("values", ["fp64", "fp32-copy"])
+def test_hierarchy_and_apply_match_restatement(Nx, Ny, k, cut, values, monkeypatch):
+    # the V-cycle's own SpMVs stream a single-precision COPY of the matrix values by default (vectors and sums in double);
+    # PB_MG_FP64 keeps them on the double values: that variant is the restatement to 1e-8, the default one to fp32 rounding
+    if values == "fp64":
+        monkeypatch.setenv("PB_MG_FP64", "1")
+    else:
+        monkeypatch.delenv("PB_MG_FP64", raising=False)
     ctx = gpu_system(Nx, Ny, k, cut)
     m, S, Sc, g = mg_ref.condensed_system(Nx, k, cut=cut, Ny=Ny)
     info = m.cut_info() if cut else None
@@ -53,7 +60,10 @@ def test_hierarchy_and_apply_match_restatement(Nx, Ny, k, cut):
     for _ in range(2):
         r = rng.standard_normal(ctx.n_rows)
         z = ctx.mg_apply(r); zr = ref(r)
-        assert np.linalg.norm(z - zr) < 1e-8 * np.linalg.norm(zr)
+        # (cut cells: the 1/area-scaled stabilisation makes D^-1 A badly conditioned, which amplifies the 6e-8 rounding of the copy)
+        err = np.linalg.norm(z - zr) / np.linalg.norm(zr)
+        assert err < (1e-8 if values == "fp64" else (1e-3 if cut else 5e-6)), err
+        print(f"mg_apply {values} {Nx}x{Ny} k={k} cut={cut}: relative difference to the restatement {err:.2e}")
     ctx.close()
 
 
