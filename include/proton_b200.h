@@ -180,7 +180,16 @@ pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
  * on uncut cells, make_hho_laplacian_interface (:390-502) + make_hho_cut_stabilization on both sides (:1689-1706) + make_rhs
  * on both sides on cut cells, then interface_assembler::assemble / assemble_cut / finalize (:1197-1340, 1430-1434) onto the
  * condensed face system in interface_assembler's numbering: unknown (f, a) = face_table[f]*fbs + a, the second set of a cut
- * face fbs further (:1161-1175, 1301).  Whole-mesh contexts, HHO(k+1,k), k <= 2, kappa_1 = kappa_2 = 1 (params<T>, :293-299).
+ * face fbs further (:1161-1175, 1301).  HHO(k+1,k), k <= 2, kappa_1 = kappa_2 = 1 (params<T>, :293-299).
+ * Strips: face_table is monotone in the face id, so a strip of cell rows owns the contiguous slots of its faces and
+ * pb_assemble / pb_get_csr / pb_pcg / pb_get_face_solution / pb_error_norms (partial sum over the owned cells) work on strip
+ * contexts as for the other problems; columns are global unknowns of the interface system.  The one global quantity, the number of
+ * cut faces owned by the strips below, is all-reduced inside pb_assemble by the ranks of a communicator (pb_dist_init); strip
+ * contexts WITHOUT one (several strips driven by one process) are told: pb_interface_cut_faces_owned after the cut preprocessing,
+ * the host's prefix sum, pb_interface_set_cut_offsets(before, total) before pb_assemble.  pb_interface_strip_layout: out =
+ * { first owned slot, one past the last, first / one-past-last referenced slot, slots of the whole system, block rows the lower /
+ * the upper neighbour reads of this strip }.  pb_recover, pb_sample_solution and pb_interface_get_local stay whole-mesh calls;
+ * pb_interface_face_table reports the faces outside the strip's window as -2.
  * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems.  pb_recover returns interface_assembler's solution
  * layout: (ncells + ncut) cell blocks of cbs in cell_table order (a cut cell carries its negative, then its positive set,
  * :1143-1160), then the face unknowns; pb_error_norms out[0] = the driver's H1 error^2 over both parts (:1775-1833);
@@ -190,6 +199,9 @@ pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
  * face_table per face, -1 for Dirichlet faces. ---- */
 pb_status pb_interface_get_local(pb_ctx* ctx, int what, double* out);
 pb_status pb_interface_face_table(pb_ctx* ctx, long long* table);
+pb_status pb_interface_cut_faces_owned(pb_ctx* ctx, long long* count);
+pb_status pb_interface_set_cut_offsets(pb_ctx* ctx, long long cut_faces_before, long long cut_faces_total);
+pb_status pb_interface_strip_layout(pb_ctx* ctx, long long out[7]);
 
 /* ---- driver outputs.
  * pb_pcg_history(capacity > 0): the following pb_pcg calls record nr/nr0 exactly where conjugated_gradient writes a line

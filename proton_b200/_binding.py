@@ -70,6 +70,9 @@ def lib():
         L.pb_pipeline_sync.argtypes = [C.c_void_p]
         L.pb_interface_get_local.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.pb_interface_face_table.argtypes = [C.c_void_p, C.c_void_p]
+        L.pb_interface_cut_faces_owned.argtypes = [C.c_void_p, C.c_void_p]
+        L.pb_interface_set_cut_offsets.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong]
+        L.pb_interface_strip_layout.argtypes = [C.c_void_p, C.c_void_p]
         L.pb_pcg_history.argtypes = [C.c_void_p, C.c_longlong]
         L.pb_pcg_get_history.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
         L.pb_sample_solution.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
@@ -321,6 +324,21 @@ class Context:
         t = np.zeros(self.nfaces, np.int64)
         self._ck(lib().pb_interface_face_table(self._h, _ptr(t)))
         return t
+
+    def interface_cut_faces_owned(self):
+        """cut faces among the faces this (strip) context owns, after the cut preprocessing"""
+        k = C.c_longlong(0)
+        self._ck(lib().pb_interface_cut_faces_owned(self._h, C.byref(k)))
+        return k.value
+
+    def interface_set_cut_offsets(self, before, total):
+        """strip contexts without a communicator: cut faces owned by the strips below this one / by all strips"""
+        self._ck(lib().pb_interface_set_cut_offsets(self._h, int(before), int(total))); return self
+
+    def interface_strip_layout(self):
+        o = (C.c_longlong * 7)()
+        self._ck(lib().pb_interface_strip_layout(self._h, o))
+        return dict(slot_begin=o[0], slot_end=o[1], slot_lo=o[2], slot_hi=o[3], slots=o[4], halo_prev=o[5], halo_next=o[6])
 
     # ---- driver outputs (SURVEY 8f.5)
     def pcg_history(self, capacity):

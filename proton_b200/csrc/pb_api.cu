@@ -59,7 +59,13 @@ struct pb_ctx {
     long long* rowptr = nullptr; int* col = nullptr; double *val = nullptr, *rhs = nullptr;
     // interface problem (pb_api_interface.inl): per-cut-cell blocks, face_table, general-CSR flag
     double *Sx = nullptr, *gx = nullptr, *recAx = nullptr, *recbx = nullptr, *lcx = nullptr, *fx = nullptr;
-    int* ftab = nullptr; bool general_csr = false;
+    int* ftab = nullptr; int* ftab_a = nullptr; bool general_csr = false;      // ftab: indexed by GLOBAL face id over the face window [fw0, fw1] (ftab_a shifted back)
+    long long ifc_cut_before = -1, ifc_cut_total = -1;      // strips: cut faces owned by the strips below / by all strips (pb_interface_set_cut_offsets, or all-reduced)
+    long long ifc_nglob = 0;                                 // unknowns of the whole interface system (modulus of the sort keys)
+    // block rows of the system this context owns [rb_begin, rb_end) and references [rb_lo, rb_hi), in the numbering of the assembled
+    // problem (plain / fictitious domain: compressed faces = strip.cf_*, col_*; interface: face_table slots), and the block rows its
+    // neighbours need (halo_prev: my first face row, the upper halo of rank-1; halo_next: my last face row, the lower halo of rank+1)
+    long long rb_begin = 0, rb_end = 0, rb_lo = 0, rb_hi = 0, halo_prev = 0, halo_next = 0;
     int* irr_rows = nullptr; int n_irr_rows = 0; int* irr_faces = nullptr; int n_irr_faces = 0; bool ifc_struct_ok = false;
     unsigned long long *ifc_k0 = nullptr, *ifc_k1 = nullptr; double *ifc_v0 = nullptr, *ifc_v1 = nullptr; long long* ifc_dnum = nullptr;
     void* ifc_tmp = nullptr; size_t ifc_tmp_bytes = 0; long long ifc_T = 0, ifc_ncut_alloc = 0;       // block rows of the cut cells' faces (scalar SpMV pass)
@@ -177,7 +183,7 @@ static void free_solver(pb_ctx* c) {
 }
 static void free_system(pb_ctx* c) {
     dfree(&c->S); dfree(&c->g); dfree(&c->recA); dfree(&c->recb); dfree(&c->lc); dfree(&c->oper); dfree(&c->rhsloc); dfree(&c->data);
-    dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab); dfree(&c->irr_rows); c->n_irr_rows = 0; dfree(&c->irr_faces); c->n_irr_faces = 0; c->ifc_struct_ok = false;
+    dfree(&c->Sx); dfree(&c->gx); dfree(&c->recAx); dfree(&c->recbx); dfree(&c->lcx); dfree(&c->fx); dfree(&c->ftab_a); c->ftab = nullptr; dfree(&c->irr_rows); c->n_irr_rows = 0; dfree(&c->irr_faces); c->n_irr_faces = 0; c->ifc_struct_ok = false;
     dfree(&c->ifc_k0); dfree(&c->ifc_k1); dfree(&c->ifc_v0); dfree(&c->ifc_v1); dfree(&c->ifc_dnum); if (c->ifc_tmp) { cudaFree(c->ifc_tmp); c->ifc_tmp = nullptr; } c->ifc_T = 0; c->ifc_ncut_alloc = 0; c->general_csr = false;
     dfree(&c->brows); dfree(&c->brp); dfree(&c->rowptr); dfree(&c->col); dfree(&c->val); dfree(&c->rhs);
     free_solver(c);
@@ -368,6 +374,12 @@ static pb_status build_structure(pb_ctx* ctx) {
     const long long nbr = ctx->strip.cf_end - ctx->strip.cf_begin;
     const int F = ctx->F;
     ctx->nrows_blk = nbr; ctx->nrows = nbr * F;
+    {   // owned / referenced block rows and what the neighbours need of them (see halo_exchange)
+        const Grid& g = ctx->grid; const Strip& s = ctx->strip;
+        ctx->rb_begin = s.cf_begin; ctx->rb_end = s.cf_end; ctx->rb_lo = s.col_lo; ctx->rb_hi = s.col_hi;
+        ctx->halo_prev = std::min(s.cf_begin + (2 * g.Nx - 1), num_free_faces(g)) - s.cf_begin;
+        ctx->halo_next = s.cf_end - compress_row_start(g, g.row_end - 1);
+    }
     int* nb = nullptr;
     CK(dalloc(ctx, &ctx->brows, (size_t)nbr)); CK(dalloc(ctx, &ctx->brp, (size_t)nbr + 1));
     CK(cudaMalloc((void**)&nb, (size_t)(nbr + 1) * 4));
@@ -474,7 +486,6 @@ static pb_status assemble_step(pb_ctx* ctx, const pb_assembly_params* p, const d
     if (ifc) {
         NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: the interface problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");
         NEED(ctx->quad_kind == PB_QUAD_POLY_DUNAVANT, PB_ERR_INVALID, "pb_assemble: the interface problem runs on the cuthho_poly mesh (PB_QUAD_POLY_DUNAVANT)");
-        NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_assemble: the interface problem is built for whole-mesh contexts");
         NEED(p->stab_kind != PB_STAB_FANCY, PB_ERR_INVALID, "pb_assemble: the interface driver uses the naive / cut stabilisation");
     }
     if (p->problem == PB_PROBLEM_FICTDOM) NEED(ctx->have_cut && ctx->have_ls, PB_ERR_STATE, "pb_assemble: fictitious-domain problem needs pb_cut_levelset and pb_cut_preprocess / pb_cut_upload first");

@@ -82,12 +82,10 @@ extern "C" pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsign
 static pb_status halo_exchange(pb_ctx* ctx, double* full, cudaStream_t stream = nullptr) {
     if (ctx->world == 1) return PB_OK;
     if (!stream) stream = ctx->stream;
-    const Grid& g = ctx->grid; const Strip& s = ctx->strip; const int F = ctx->F;
-    const long long n = ctx->nrows, down = (s.cf_begin - s.col_lo) * F, up = (s.col_hi - s.cf_end) * F;
-    const long long nfree = num_free_faces(g);
-    long long to_prev = s.cf_begin + (2 * g.Nx - 1); if (to_prev > nfree) to_prev = nfree;
-    to_prev = (to_prev - s.cf_begin) * F;                                       // upper halo of rank r-1
-    const long long to_next = (s.cf_end - compress_row_start(g, g.row_end - 1)) * F;   // lower halo of rank r+1: my last face row
+    const int F = ctx->F;
+    const long long n = ctx->nrows, down = (ctx->rb_begin - ctx->rb_lo) * F, up = (ctx->rb_hi - ctx->rb_end) * F;
+    const long long to_prev = ctx->halo_prev * F;        // upper halo of rank r-1: my first face row
+    const long long to_next = ctx->halo_next * F;        // lower halo of rank r+1: my last face row
     double* own = full + down;
     NCK(nccl_dl::g.GroupStart());
     if (ctx->rank > 0) {
@@ -99,6 +97,22 @@ static pb_status halo_exchange(pb_ctx* ctx, double* full, cudaStream_t stream = 
         NCK(nccl_dl::g.Recv(own + n, (size_t)up, nccl_dl::Float64, ctx->rank + 1, ctx->comm, stream));
     }
     NCK(nccl_dl::g.GroupEnd());
+    return PB_OK;
+}
+
+// every rank contributes one count (interface problem: the cut faces it owns): sum over the ranks below this one, and over all
+static pb_status dist_gather_counts(pb_ctx* ctx, long long mine, long long* before, long long* total) {
+    const int W = ctx->world;
+    double* d = nullptr;
+    struct Cleanup { double*& d; ~Cleanup() { cudaFree(d); } } cleanup{d};
+    CK(cudaMalloc((void**)&d, (size_t)W * 8));
+    std::vector<double> h((size_t)W, 0.0); h[(size_t)ctx->rank] = (double)mine;      // counts are far below 2^53: exact in double
+    CK(cudaMemcpyAsync(d, h.data(), (size_t)W * 8, cudaMemcpyHostToDevice, ctx->stream));
+    NCK(nccl_dl::g.AllReduce(d, d, (size_t)W, nccl_dl::Float64, nccl_dl::Sum, ctx->comm, ctx->stream));
+    CK(cudaMemcpyAsync(h.data(), d, (size_t)W * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *before = 0; *total = 0;
+    for (int q = 0; q < W; q++) { if (q < ctx->rank) *before += (long long)h[(size_t)q]; *total += (long long)h[(size_t)q]; }
     return PB_OK;
 }
 
@@ -116,7 +130,7 @@ static int spmv_lanes(int F) { int len = 7 * F; return len <= 8 ? 4 : len <= 16 
 // another cut, ...), so no entry point can run on a partly allocated or stale-sized set
 static pb_status ensure_solver(pb_ctx* ctx) {
     const long long n = ctx->nrows; const int F = ctx->F;
-    const long long nfull = ctx->general_csr ? n : (ctx->strip.col_hi - ctx->strip.col_lo) * F;      // interface problem: whole mesh, its own numbering
+    const long long nfull = (ctx->rb_hi - ctx->rb_lo) * F;
     const bool ok = ctx->solver_n == n && ctx->solver_nfull == nfull && ctx->x && ctx->r && ctx->z && ctx->dfull && ctx->y && ctx->iA && ctx->parts && ctx->scal;
     if (!ok) {
         free_solver(ctx);
@@ -127,7 +141,7 @@ static pb_status ensure_solver(pb_ctx* ctx) {
         CK(cudaMemsetAsync(ctx->x, 0, (size_t)n * 8, ctx->stream));
         ctx->solver_n = n; ctx->solver_nfull = nfull;
     }
-    ctx->d = ctx->dfull + (ctx->general_csr ? 0 : (ctx->strip.cf_begin - ctx->strip.col_lo) * F);
+    ctx->d = ctx->dfull + (ctx->rb_begin - ctx->rb_lo) * F;
     return PB_OK;
 }
 static pb_status ensure_block_inverse(pb_ctx* ctx) {
@@ -148,7 +162,7 @@ struct SpmvPlan {
 static SpmvPlan make_spmv_plan(pb_ctx* ctx) {
     SpmvPlan P{};
     const int F = ctx->F; const long long n = ctx->nrows;
-    P.n = n; P.F = F; P.xoff = ctx->general_csr ? 0 : ctx->strip.col_lo * F; P.down = ctx->general_csr ? 0 : (ctx->strip.cf_begin - ctx->strip.col_lo) * F;
+    P.n = n; P.F = F; P.xoff = ctx->rb_lo * F; P.down = (ctx->rb_begin - ctx->rb_lo) * F;
     int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
     int nblk = nsm * 8; if (nblk > PCG_MAX_BLOCKS) nblk = PCG_MAX_BLOCKS;
     const long long want = (n + PCG_THREADS - 1) / PCG_THREADS; if (want < nblk) nblk = (int)(want < 1 ? 1 : want);
@@ -228,7 +242,7 @@ static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull
         switch (F) { case 1: PB_SPMV(8, 1, 0); break; case 2: PB_SPMV(8, 2, 0); break; case 3: PB_SPMV(8, 3, 0); break; default: PB_SPMV(8, 4, 0); break; }
     }
 #undef PB_SPMV
-    if (P.nblk_irr) pcg_spmv_rows_kernel<<<P.nblk_irr, PCG_THREADS, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rowptr, ctx->col, ctx->val, vfull, y, p_dy + P.nblk_sp, ctx->cg);
+    if (P.nblk_irr) pcg_spmv_rows_kernel<<<P.nblk_irr, PCG_THREADS, 0, sm>>>(ctx->n_irr_rows, F, ctx->irr_rows, ctx->rowptr, ctx->col, ctx->val, vfull - P.xoff, P.xoff + P.down, y, p_dy + P.nblk_sp, ctx->cg);
     CK(cudaGetLastError());
     return PB_OK;
 }
@@ -271,12 +285,12 @@ extern "C" pb_status pb_pcg(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* re
     auto t0 = std::chrono::steady_clock::now();
     CK(cudaEventRecord(ctx->ev[0], sm));
     if (blockpre) {
-#define PB_BJ(F_) do { pcg_bdiag_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iAb); \
+#define PB_BJ(F_) do { pcg_bdiag_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, ctx->rb_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iAb); \
         pcg_init_blk_kernel<F_><<<nblk, PCG_THREADS, 0, sm>>>(nbr_own, ctx->rhs, ctx->iAb, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz); } while (0)
         if (F == 2) PB_BJ(2); else if (F == 3) PB_BJ(3); else PB_BJ(4);
 #undef PB_BJ
     } else {
-        pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->general_csr ? 0 : ctx->strip.cf_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
+        pcg_diag_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, ctx->rb_begin * F, ctx->rowptr, ctx->col, ctx->val, ctx->iA);
         pcg_init_kernel<<<nblk, PCG_THREADS, 0, sm>>>(n, pre, ctx->rhs, ctx->iA, ctx->x, ctx->r, ctx->z, ctx->d, p_rr, p_rz);
     }
     { pb_status st = reduce_rr_rz(); if (st != PB_OK) return st; }

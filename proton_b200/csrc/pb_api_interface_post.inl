@@ -2,9 +2,10 @@
 // (cell unknowns with cell_table, cut cells twice: negative then positive part, cuthho_square.cpp:1143-1151, 1343-1365;
 // then the face unknowns) and the driver's H1 error (run_cuthho_interface, :1769-1837).
 
-__global__ void ifc_gather_regular_kernel(Grid g, int F, const int* __restrict__ ftab, const double* __restrict__ x, double* __restrict__ xreg) {
-    const long long nc = g.Nx * g.Ny;
-    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < nc; c += (long long)gridDim.x * blockDim.x) {
+// (cells [c_begin, c_end) = the owned cells; x is addressed by global unknown of the interface system, xreg by global compressed
+//  face unknown: both through pointers shifted back by the first column this context holds)
+__global__ void ifc_gather_regular_kernel(Grid g, int F, long long c_begin, long long c_end, const int* __restrict__ ftab, const double* __restrict__ x, double* __restrict__ xreg) {
+    for (long long c = c_begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; c < c_end; c += (long long)gridDim.x * blockDim.x) {
         const long long ci = c % g.Nx, cj = c / g.Nx;
         long long f[4]; cell_faces(g, ci, cj, f);
         for (int li = 0; li < 4; li++) {
@@ -14,11 +15,12 @@ __global__ void ifc_gather_regular_kernel(Grid g, int F, const int* __restrict__
         }
     }
 }
-__global__ void ifc_recover_cut_kernel(Grid g, int F, int C, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ face_loc,
+// cut slots [slot0, ncut) = the owned cut cells of the window list
+__global__ void ifc_recover_cut_kernel(Grid g, int F, int C, int slot0, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ face_loc,
                                        const int* __restrict__ ftab, const double* __restrict__ recAx, const double* __restrict__ recbx,
                                        const double* __restrict__ x, double* __restrict__ ucut) {
     const int C2 = 2 * C, NF2 = 8 * F;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)ncut * C2; t += (long long)gridDim.x * blockDim.x) {
+    for (long long t = (long long)slot0 * C2 + blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)ncut * C2; t += (long long)gridDim.x * blockDim.x) {
         const long long slot = t / C2; const int a = (int)(t - slot * C2);
         const long long c = cut_cells[slot], ci = c % g.Nx, cj = c / g.Nx;
         long long f[4]; cell_faces(g, ci, cj, f);
@@ -44,15 +46,15 @@ __global__ void ifc_pack_cells_kernel(Grid g, int C, int ncut, const int* __rest
 template <int CD>
 __global__ void __launch_bounds__(32) interface_h1_kernel(Grid g, const double2* __restrict__ points, const int* __restrict__ node_loc,
                                                            const int* __restrict__ cell_loc, const int* __restrict__ cut_cells, const double2* __restrict__ iface,
-                                                           int ncut, int NI, int fun, const double* __restrict__ uc, const double* __restrict__ ucut,
-                                                           double* __restrict__ parts) {
+                                                           int ncut, int NI, int fun, long long c_begin, long long c_end, const double* __restrict__ uc,
+                                                           const double* __restrict__ ucut, double* __restrict__ parts) {
+    // (cells [c_begin, c_end) = the owned cells; uc is addressed by global cell id through a shifted pointer)
     constexpr int C = cell_basis_size(CD);
     __shared__ double tp[2 * CUT_MAX_TP];
     __shared__ int s_ntp;
     const int lane = threadIdx.x;
-    const long long nc = g.Nx * g.Ny;
     double sum = 0.0;
-    for (long long c = blockIdx.x; c < nc; c += gridDim.x) {
+    for (long long c = c_begin + blockIdx.x; c < c_end; c += gridDim.x) {
         const long long ci = c % g.Nx, cj = c / g.Nx, p0 = grid_point(g, ci, cj);
         const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
         CellGeom geo; int nloc[4];
@@ -208,6 +210,7 @@ __global__ void __launch_bounds__(32) interface_sample_kernel(Grid g, const doub
 }
 
 static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
+    NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_sample_solution (interface): whole-mesh contexts");
     const Grid& g = ctx->grid; const int CD = ctx->CD;
     const long long nc = g.Nx * g.Ny;
     const int np = dunavant_npts(2 * CD);
@@ -231,28 +234,41 @@ static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_p
     return PB_OK;
 }
 
-// cell unknowns of all cells (uc: regular cell order; ucut: [u-, u+] per cut slot) from the face solution ctx->x
+// cell unknowns of the owned cells from the face solution ctx->x (uc: owned cells in order, *uc_out is the allocation; ucut:
+// [u-, u+] per cut slot of the window list, filled for the owned cut cells).  Strips fetch the halo part of x first.
 static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** ucut_out) {
-    const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C;
-    const long long nc = g.Nx * g.Ny, nreg = num_free_faces(g) * F;
-    double *xreg = nullptr, *uc = nullptr, *ucut = nullptr;
-    CK(cudaMalloc((void**)&xreg, (size_t)nreg * 8)); CK(cudaMalloc((void**)&uc, (size_t)nc * C * 8));
-    CK(cudaMalloc((void**)&ucut, (size_t)(ctx->ncut > 0 ? ctx->ncut : 1) * 2 * C * 8));
-    ifc_gather_regular_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, F, ctx->ftab, ctx->x, xreg);
-#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, 0, nc, 0, C, ctx->prm.fun, ctx->points, ctx->recA, ctx->recb, xreg, 0, uc, nullptr)
+    const Grid& g = ctx->grid; const int F = ctx->F, C = ctx->C; const Strip& st = ctx->strip;
+    const long long c_begin = g.row_begin * g.Nx, c_end = g.row_end * g.Nx, owned = c_end - c_begin;
+    const long long nreg = (st.col_hi - st.col_lo) * F, nfull = (ctx->rb_hi - ctx->rb_lo) * F, down = (ctx->rb_begin - ctx->rb_lo) * F;
+    double *xs = nullptr, *xreg = nullptr, *uc = nullptr, *ucut = nullptr;
+    auto release = [&]() { cudaFree(xs); cudaFree(xreg); cudaFree(uc); cudaFree(ucut); };
+#define IFP(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { release(); return fail(ctx, PB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } } while (0)
+    IFP(cudaMalloc((void**)&xs, (size_t)nfull * 8)); IFP(cudaMalloc((void**)&xreg, (size_t)nreg * 8)); IFP(cudaMalloc((void**)&uc, (size_t)owned * C * 8));
+    IFP(cudaMalloc((void**)&ucut, (size_t)(ctx->ncut > 0 ? ctx->ncut : 1) * 2 * C * 8));
+    IFP(cudaMemsetAsync(xs, 0, (size_t)nfull * 8, ctx->stream)); IFP(cudaMemsetAsync(xreg, 0, (size_t)nreg * 8, ctx->stream));
+    IFP(cudaMemsetAsync(ucut, 0, (size_t)(ctx->ncut > 0 ? ctx->ncut : 1) * 2 * C * 8, ctx->stream));
+    IFP(cudaMemcpyAsync(xs + down, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    { pb_status s2 = halo_exchange(ctx, xs); if (s2 != PB_OK) { release(); return s2; } }
+    const double* xsg = xs - ctx->rb_lo * F;                 // by global unknown of the interface system
+    ifc_gather_regular_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, F, c_begin, c_end, ctx->ftab, xsg, xreg - st.col_lo * F);
+    double* uc_shift = uc - c_begin * C;                     // K6 indexes cell dofs by GLOBAL cell id
+#define PB_REC(FD_) recover_kernel<FD_><<<148 * 4, 128, 0, ctx->stream>>>(g, st.cell_row0, ctx->ncells_local, g.row_begin, C, ctx->prm.fun, ctx->points, ctx->recA, ctx->recb, \
+                                                                         xreg, st.col_lo * F, uc_shift, nullptr)
     switch (ctx->FD) { case 0: PB_REC(0); break; case 1: PB_REC(1); break; default: PB_REC(2); break; }
 #undef PB_REC
-    if (ctx->ncut > 0)
-        ifc_recover_cut_kernel<<<148 * 2, 256, 0, ctx->stream>>>(g, F, C, ctx->ncut, ctx->cut_cells, ctx->face_loc, ctx->ftab, ctx->recAx, ctx->recbx, ctx->x, ucut);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(xreg);
-    if (e != cudaSuccess) { cudaFree(uc); cudaFree(ucut); return fail(ctx, PB_ERR_CUDA, "interface back-substitution failed: %s", cudaGetErrorString(e)); }
+    if (ctx->ncut_owned > 0)
+        ifc_recover_cut_kernel<<<148 * 2, 256, 0, ctx->stream>>>(g, F, C, ctx->ncut - ctx->ncut_owned, ctx->ncut, ctx->cut_cells, ctx->face_loc, ctx->ftab, ctx->recAx, ctx->recbx, xsg, ucut);
+    IFP(cudaGetLastError());
+    IFP(cudaStreamSynchronize(ctx->stream));
+#undef IFP
+    cudaFree(xs); cudaFree(xreg);
     *uc_out = uc; *ucut_out = ucut;
     return PB_OK;
 }
 
 static pb_status interface_recover(pb_ctx* ctx, double* full) {
+    NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED,
+         "pb_recover (interface): the reference's full vector is assembled on whole-mesh contexts (strips: pb_error_norms, pb_get_face_solution)");
     const Grid& g = ctx->grid; const int C = ctx->C;
     const long long nc = g.Nx * g.Ny, ncell_dofs = (nc + ctx->ncut) * C;
     double *uc = nullptr, *ucut = nullptr, *packed = nullptr;
@@ -275,7 +291,7 @@ static pb_status interface_error(pb_ctx* ctx, double out[3]) {
     const int grid = 148 * 16;
     CK(cudaMalloc((void**)&parts, (size_t)grid * 8));
 #define PB_H1(CD_) interface_h1_kernel<CD_><<<grid, 32, 0, ctx->stream>>>(g, ctx->points, ctx->node_loc, ctx->cell_loc_g, ctx->cut_cells, ctx->iface, ctx->ncut, ctx->NI, \
-                                                                         ctx->prm.fun, uc, ucut, parts)
+                                                                         ctx->prm.fun, g.row_begin * g.Nx, g.row_end * g.Nx, uc - g.row_begin * g.Nx * ctx->C, ucut, parts)
     switch (ctx->CD) { case 1: PB_H1(1); break; case 2: PB_H1(2); break; default: PB_H1(3); break; }
 #undef PB_H1
     std::vector<double> h((size_t)grid);

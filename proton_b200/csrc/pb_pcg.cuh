@@ -170,8 +170,10 @@ __global__ void pcg_spmv_blk_kernel(long long n, long long xoff, const BlockRow*
 // scalar rows of a short list of block rows (interface problem: the rows of the cut cells' faces, which the block kernel
 // leaves at zero); one thread per scalar row, partial sums of d.y appended after the block kernel's
 __global__ void pcg_spmv_rows_kernel(int nbrows, int F, const int* __restrict__ brow_list, const long long* __restrict__ rowptr, const int* __restrict__ col,
-                                     const double* __restrict__ val, const double* __restrict__ dvec, double* __restrict__ y, double* __restrict__ parts_dy,
-                                     const CgState* st) {
+                                     const double* __restrict__ val, const double* __restrict__ dvec, long long row0, double* __restrict__ y,
+                                     double* __restrict__ parts_dy, const CgState* st) {
+    // dvec is indexed by GLOBAL unknown (the caller shifts the halo'd vector back by its first column); the listed rows and y are
+    // local to the owned rows, which start at global unknown row0
     __shared__ double sh[32];
     if (st->done) return;
     const int lane = threadIdx.x & 31, nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -182,7 +184,7 @@ __global__ void pcg_spmv_rows_kernel(int nbrows, int F, const int* __restrict__ 
         for (long long k = rowptr[r] + lane; k < rowptr[r + 1]; k += 32) acc += val[k] * dvec[col[k]];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-        if (lane == 0) { y[r] = acc; dy += acc * dvec[r]; }
+        if (lane == 0) { y[r] = acc; dy += acc * dvec[row0 + r]; }
     }
     double t = block_reduce_sum(dy, sh); if (threadIdx.x == 0) parts_dy[blockIdx.x] = t;
 }

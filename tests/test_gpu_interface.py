@@ -213,3 +213,60 @@ def test_interface_solution_samples_match_the_driver_dat_rows(ctx, k, N):
     assert got.shape == want.shape
     assert np.max(np.abs(got[:, :2] - want[:, :2])) < 1e-13
     assert np.max(np.abs(got[:, 2] - want[:, 2])) < 1e-11 * max(1.0, np.max(np.abs(want[:, 2])))
+
+
+@pytest.mark.parametrize("k,N,cuts", [(1, 20, (0, 7, 13, 20)), (2, 16, (0, 3, 8, 16)), (0, 33, (0, 5, 17, 18, 33)), (1, 24, (0, 12, 24)), (2, 20, (0, 4, 5, 6, 20))])
+def test_interface_strip_contexts_assemble_the_same_rows(k, N, cuts):
+    """multi-GPU partition of the interface problem (SURVEY 8e on 8f.3): face_table is monotone in the face id, so every strip of
+    cell rows owns a contiguous range of slots.  Each strip context preprocesses its window of the level set, is told the cut
+    faces of the strips below it (what the ranks of a communicator all-reduce), assembles its rows — regular ones by K3,
+    the cut cells' faces from sorted triplets — and reproduces the whole-mesh rows, columns, values and rhs bit for bit."""
+    hdi = pb.hho_degree_info(k + 1, k); F = hdi.fbs
+    whole = pb.Context(0)
+    whole.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT)
+    whole.cut_levelset(0, 0.35, 0.5, 0.5); whole.cut_preprocess(4)
+    whole.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+    rp, col, val, rhs = whole.csr()
+    ft = whole.interface_face_table()
+    LW = whole.interface_strip_layout()
+    assert LW["slot_begin"] == 0 and LW["slot_end"] == LW["slots"] == whole.n_rows // F
+    strips = []
+    for rb, re in zip(cuts[:-1], cuts[1:]):
+        c = pb.Context(0)
+        c.mesh(pb.mesh_init_params(N, N), quad_kind=PB.QUAD_POLY_DUNAVANT, row_begin=rb, row_end=re)
+        c.cut_levelset(0, 0.35, 0.5, 0.5); c.cut_preprocess(4)
+        strips.append((c, rb, re, c.interface_cut_faces_owned()))
+    total = sum(s[3] for s in strips)
+    assert total == LW["slots"] - pb.strip_layout(N, N, 0, N, F)["cf_end"]            # every cut face is owned by exactly one strip
+    # a strip that is not told about the others refuses to number its rows
+    with pytest.raises(pb.ProtonError):
+        strips[1][0].assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+    before = 0; next_slot = 0
+    for c, rb, re, mine in strips:
+        c.interface_set_cut_offsets(before, total)
+        c.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        L = c.interface_strip_layout()
+        assert L["slot_begin"] == next_slot and L["slots"] == LW["slots"]
+        assert L["slot_lo"] <= L["slot_begin"] <= L["slot_end"] <= L["slot_hi"]
+        next_slot = L["slot_end"]
+        rp_s, col_s, val_s, rhs_s = c.csr()
+        r0 = L["slot_begin"] * F
+        assert c.n_rows == (L["slot_end"] - L["slot_begin"]) * F
+        lo, hi = rp[r0], rp[r0 + c.n_rows]
+        assert np.array_equal(rp_s, rp[r0 : r0 + c.n_rows + 1] - lo)
+        assert np.array_equal(col_s, col[lo:hi])
+        assert np.array_equal(val_s, val[lo:hi])
+        assert np.array_equal(rhs_s, rhs[r0 : r0 + c.n_rows])
+        # every referenced column lies in the halo'd range the solver vectors hold
+        assert col_s.min() >= L["slot_lo"] * F and col_s.max() < L["slot_hi"] * F
+        # face_table of the strip = the whole one inside its window, -2 outside
+        fts = c.interface_face_table()
+        inside = fts != -2
+        assert np.array_equal(fts[inside], ft[inside]) and inside.sum() > 0
+        # second assembly reuses the structure and gives the same values
+        c.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        assert np.array_equal(c.csr()[2], val_s)
+        before += mine
+        c.close()
+    assert next_slot == LW["slots"]
+    whole.close()
