@@ -96,6 +96,34 @@ def main():
             print(f"rank {rank}: multigrid fictdom solve differs (N={N} k={k}): {rm}", flush=True)
         ok = ok and okm
         ctx.close()
+    # two-material interface problem (doubled unknowns on cut faces): every strip owns the contiguous slots of its faces; the cut
+    # faces of the strips below are all-reduced inside pb_assemble; halos are slot ranges; H1 error summed over the ranks
+    for (N, k) in [(24, 1), (33, 0), (32, 2), (128, 2)]:
+        mip = pb.mesh_init_params(N, N)
+        hdi = pb.hho_degree_info(k + 1, k)
+        ctx = make_rank_context(mip, PB.QUAD_POLY_DUNAVANT, rank, world, lr, dist)
+        ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        L = ctx.interface_strip_layout()
+        res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 200000, True))
+        faces = ctx.face_solution()
+        et = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{lr}"); dist.all_reduce(et)
+        gf = [None] * world; gl = [None] * world
+        dist.all_gather_object(gf, faces); dist.all_gather_object(gl, (L["slot_begin"], L["slot_end"], L["slots"]))
+        if rank == 0:
+            ref = pb.Context(lr)
+            ref.mesh(mip, PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
+            ref.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+            r1 = ref.conjugated_gradient(pb.cg_params(1e-13, 1e8, 200000, True))
+            x1 = ref.face_solution(); e1 = ref.error_norms()[0]
+            got = np.concatenate(gf)
+            contiguous = gl[0][0] == 0 and all(gl[i][1] == gl[i + 1][0] for i in range(world - 1)) and gl[-1][1] == gl[-1][2] == ref.n_rows // hdi.fbs
+            err = np.linalg.norm(got - x1) / np.linalg.norm(x1) if got.shape == x1.shape else float("inf")
+            print(f"interface N={N} k={k} world={world}: unknowns {ref.n_rows}, iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, "
+                  f"rel diff {err:.2e}, H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
+            ok = ok and contiguous and err < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2 and abs(float(et[0]) - e1) <= 1e-8 * e1
+            ref.close()
+        ctx.close()
     flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ok = bool(int(flag))
