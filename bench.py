@@ -287,15 +287,28 @@ def obstacle_record(args, dev, pb, PB):
     return out
 
 
-def interface_record(args, dev, pb, PB):
-    """Secondary record (single GPU): the two-material interface problem of `cuthho_square -i`, k=2, circle level
-    set r=0.35, on ifc_N x ifc_N quads: preprocessing, repeated assembly (K1 + K2i + K3 + sorted rows of the cut cells' faces), a
-    fixed number of PCG iterations."""
+def interface_record(args, rank, world, dev, dist, torch, pb, PB):
+    """Secondary record: the two-material interface problem of `cuthho_square -i`, k=2, circle level set r=0.35, on
+    ifc_N x ifc_N quads sharded by cell rows over the ranks (fixed total size; every strip owns the contiguous face_table slots of
+    its faces): preprocessing, repeated assembly (K1 + K2i + K3 + sorted rows of the cut cells' faces), a fixed number of PCG
+    iterations; times are the max over the ranks.  N > 1 adds the joint solve of a 128 x 128 problem against the one-GPU solve."""
+    import numpy as np
+    from proton_b200.dist import make_rank_context
     Nc, k = args.ifc_N, 2
     hdi = pb.hho_degree_info(k + 1, k)
-    ctx = pb.Context(dev)
-    ctx.mesh(pb.mesh_init_params(Nc, Nc), PB.QUAD_POLY_DUNAVANT)
-    ctx.cut_levelset(0, 0.35, 0.5, 0.5); ctx.cut_preprocess(4)
+
+    def allred(vals, op=None):
+        if dist is None:
+            return [float(v) for v in vals]
+        tt = torch.tensor(vals, dtype=torch.float64, device=f"cuda:{dev}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return [float(v) for v in tt.tolist()]
+
+    def make(N):
+        c = make_rank_context(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT, rank, world, dev, dist)
+        c.cut_levelset(0, 0.35, 0.5, 0.5); c.cut_preprocess(4)
+        return c
+    ctx = make(Nc)
     ms = []
     for i in range(5):
         ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
@@ -306,10 +319,33 @@ def interface_record(args, dev, pb, PB):
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 20, True))
     ctx.conjugated_gradient(pb.cg_params(0.0, 1e300, 100, True))
     it_ms = ctx.timings()["ms_pcg"] / 101.0
-    out = {"workload": f"cutHHO two-material interface problem (cuthho_square -i) k=2, circle level set r=0.35, {Nc}x{Nc} quads, one GPU",
-           "cut_cells": ctx.cut_counts()[0], "unknowns": ctx.n_rows, "nnz": ctx.nnz, "local_ms": loc, "system_ms": sysb,
+    loc, sysb, it_ms = allred([loc, sysb, it_ms], "max")
+    unknowns, nnz, cut_owned = allred([ctx.n_rows, ctx.nnz, ctx.cut_counts_owned()[1]])
+    out = {"workload": f"cutHHO two-material interface problem (cuthho_square -i) k=2, circle level set r=0.35, {Nc}x{Nc} quads sharded over {world} GPU(s) by cell rows",
+           "cut_cells": int(cut_owned), "unknowns": int(unknowns), "nnz": int(nnz), "local_ms": loc, "system_ms": sysb,
            "cells_per_s": Nc * Nc / ((loc + sysb) * 1e-3), "pcg_ms_per_iter": it_ms}
     ctx.close()
+    if world > 1:
+        N = 128
+        c = make(N)
+        c.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        r = c.conjugated_gradient(pb.cg_params(1e-13, 1e8, 200000, True))
+        faces = c.face_solution(); L = c.interface_strip_layout()
+        h1 = allred([c.error_norms()[0]])[0]
+        c.close()
+        ref = pb.Context(dev)                   # every rank repeats the small one-GPU solve
+        ref.mesh(pb.mesh_init_params(N, N), PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
+        ref.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_INTERFACE)
+        r1 = ref.conjugated_gradient(pb.cg_params(1e-13, 1e8, 200000, True))
+        x1 = ref.face_solution(); e1 = float(ref.error_norms()[0])
+        ref.close()
+        mine = x1[L["slot_begin"] * hdi.fbs: L["slot_end"] * hdi.fbs]
+        d2, n2 = allred([float(np.sum((faces - mine) ** 2)), float(np.sum(mine ** 2))])
+        rel = d2 ** 0.5 / n2 ** 0.5
+        ok = r["exit_reason"] == PB.CG_CONVERGED and rel < 1e-8 and abs(h1 - e1) <= 1e-8 * e1 and abs(r["iterations"] - r1["iterations"]) <= 2
+        out["dist_check"] = {"workload": f"{N}x{N}, k=2, {world} ranks against one GPU, Jacobi-PCG to 1e-13", "passed": bool(ok), "solution_rel_diff": rel,
+                             "h1_error_sq": h1, "h1_error_sq_one_gpu": e1, "iterations": r["iterations"], "iterations_one_gpu": r1["iterations"]}
+        assert ok, f"multi-GPU interface solution differs from the one-GPU solve: {out['dist_check']}"
     return out
 
 
@@ -528,8 +564,8 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         out["dist_check"] = dist_check_record(rank, world, dev, dist, torch, pb, PB)
         assert out["dist_check"]["passed"], f"multi-GPU solution differs from the one-GPU solve: {out['dist_check']}"
-    if world == 1 and not args.no_interface:
-        out["interface"] = interface_record(args, dev, pb, PB)
+    if not args.no_interface:
+        out["interface"] = interface_record(args, rank, world, dev, dist, torch, pb, PB)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
