@@ -21,6 +21,7 @@
 #include "pb_norms.cuh"
 #include "pb_pcg.cuh"
 #include "pb_mg.cuh"
+#include "pb_mg_lines.cuh"
 #include "pb_system.cuh"
 #include "pb_generic.cuh"
 #include "pb_obstacle.cuh"

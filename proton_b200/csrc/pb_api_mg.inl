@@ -9,6 +9,7 @@ static void mg_free(pb_ctx* c) {
         dfree(&D.E); dfree(&D.st); dfree(&D.idiag); dfree(&D.x); dfree(&D.b); dfree(&D.r); dfree(&D.t);
     }
     dfree(&M.resfull); dfree(&M.zfull); dfree(&M.wfull); dfree(&M.lam); dfree(&M.valf); M.valf_n = 0;
+    if (M.fac_h) { cudaFree(M.fac_h); M.fac_h = nullptr; } if (M.fac_v) { cudaFree(M.fac_v); M.fac_v = nullptr; } dfree(&M.tl); M.fac_key[0] = M.fac_key[1] = M.fac_key[2] = 0; M.lines = false;
     M.ready = false; M.gen = -1; M.nlev = 0; M.nfull = 0; M.key[0] = M.key[1] = M.key[2] = M.key[3] = 0;
 }
 
@@ -83,6 +84,65 @@ template <int F> static void mg_launch_cheb(pb_ctx* ctx, int nblk, long long nbr
                                             const double* src, double* res, double* d, double* z) {
     mg_cheb_kernel<F><<<nblk, PCG_THREADS, 0, ctx->stream>>>(nbr, first, have_y, acc, last, c1, c2, ctx->iAb, src, ctx->y, res, d, z, ctx->cg);
 }
+// line-block Jacobi (pb_mg_lines.cuh): the problems whose stabilisation is scaled by 1/area (naive and cut stabilisation);
+// PB_MG_LINES=0 / 1 overrides
+static bool mg_wants_lines(const pb_ctx* ctx) {
+    const char* e = getenv("PB_MG_LINES");
+    if (e) return atoi(e) != 0;
+    return ctx->prm.problem == PB_PROBLEM_FICTDOM || ctx->prm.stab_kind != PB_STAB_FANCY;
+}
+template <int F, typename VT> static void mg_launch_line_factor(pb_ctx* ctx, const MgLineSet& H, const MgLineSet& V) {
+    MgState& M = ctx->mg; const long long row0 = ctx->strip.cf_begin * F;
+    for (int dir = 0; dir < 2; dir++) {
+        const MgLineSet& S = dir ? V : H; VT* fac = (VT*)(dir ? M.fac_v : M.fac_h);
+        if (S.nlines <= 0 || S.nsteps <= 0) continue;
+        mg_line_gather_kernel<F, VT><<<mg_blocks((long long)S.nlines * S.nsteps), 256, 0, ctx->stream>>>(S, row0, ctx->rowptr, ctx->col, ctx->val, fac);
+        mg_line_factor_kernel<F, VT><<<(S.nlines + 31) / 32, 32, 0, ctx->stream>>>(S, fac);
+    }
+}
+// tl = L^{-1} r (owned rows)
+template <int F, typename VT> static void mg_launch_line_solve(pb_ctx* ctx, const MgLineSet& H, const MgLineSet& V, const double* r, double* t, const CgState* st) {
+    MgState& M = ctx->mg;
+    MgLineSet A = H, B = V;
+    if (A.nsteps == 0) A.nlines = 0;
+    if (B.nsteps == 0) B.nlines = 0;
+    const int total = A.nlines + B.nlines;
+    if (total > 0) mg_line_solve_kernel<F, VT><<<(total + 31) / 32, 32, 0, ctx->stream>>>(A, (const VT*)M.fac_h, B, (const VT*)M.fac_v, r, t, st);
+}
+static void mg_line_solve(pb_ctx* ctx, const double* r, double* t, const CgState* st) {
+    MgLineSet H, V; mg_line_sets(ctx->grid, ctx->grid.row_begin, ctx->grid.row_end, ctx->strip.cf_begin, H, V);
+    const bool f64 = ctx->mg.lines_f64;
+    switch (ctx->F) {
+    case 1: if (f64) mg_launch_line_solve<1, double>(ctx, H, V, r, t, st); else mg_launch_line_solve<1, float>(ctx, H, V, r, t, st); break;
+    case 2: if (f64) mg_launch_line_solve<2, double>(ctx, H, V, r, t, st); else mg_launch_line_solve<2, float>(ctx, H, V, r, t, st); break;
+    case 3: if (f64) mg_launch_line_solve<3, double>(ctx, H, V, r, t, st); else mg_launch_line_solve<3, float>(ctx, H, V, r, t, st); break;
+    default: if (f64) mg_launch_line_solve<4, double>(ctx, H, V, r, t, st); else mg_launch_line_solve<4, float>(ctx, H, V, r, t, st); break;
+    }
+}
+// factors of the current system values
+static pb_status mg_line_setup(pb_ctx* ctx) {
+    MgState& M = ctx->mg; const int F = ctx->F;
+    MgLineSet H, V; mg_line_sets(ctx->grid, ctx->grid.row_begin, ctx->grid.row_end, ctx->strip.cf_begin, H, V);
+    const bool f64 = getenv("PB_MG_FP64") != nullptr;
+    const long long nh = (long long)H.nlines * H.nsteps, nv = (long long)V.nlines * V.nsteps;
+    NEED((nh + nv) * F == ctx->nrows, PB_ERR_STATE, "pb_pcg: the mesh lines do not cover the owned faces");
+    const long long key[3] = {nh * F * F, nv * F * F, f64 ? 8 : 4};
+    if (key[0] != M.fac_key[0] || key[1] != M.fac_key[1] || key[2] != M.fac_key[2] || !M.tl) {
+        if (M.fac_h) { cudaFree(M.fac_h); M.fac_h = nullptr; } if (M.fac_v) { cudaFree(M.fac_v); M.fac_v = nullptr; }
+        CK(cudaMalloc(&M.fac_h, (size_t)std::max<long long>(1, nh) * 2 * F * F * key[2])); CK(cudaMalloc(&M.fac_v, (size_t)std::max<long long>(1, nv) * 2 * F * F * key[2]));
+        CK(dalloc(ctx, &M.tl, (size_t)ctx->nrows));
+        for (int k = 0; k < 3; k++) M.fac_key[k] = key[k];
+    }
+    M.lines_f64 = f64;
+    switch (F) {
+    case 1: if (f64) mg_launch_line_factor<1, double>(ctx, H, V); else mg_launch_line_factor<1, float>(ctx, H, V); break;
+    case 2: if (f64) mg_launch_line_factor<2, double>(ctx, H, V); else mg_launch_line_factor<2, float>(ctx, H, V); break;
+    case 3: if (f64) mg_launch_line_factor<3, double>(ctx, H, V); else mg_launch_line_factor<3, float>(ctx, H, V); break;
+    default: if (f64) mg_launch_line_factor<4, double>(ctx, H, V); else mg_launch_line_factor<4, float>(ctx, H, V); break;
+    }
+    CK(cudaGetLastError());
+    return PB_OK;
+}
 #define PB_MG_F(call_) do { switch (ctx->F) { case 1: call_(1); break; case 2: call_(2); break; case 3: call_(3); break; default: call_(4); break; } } while (0)
 
 // operators of all levels from the current system values: block inverses, lmax, element matrices, stencils
@@ -104,6 +164,8 @@ static pb_status mg_setup(pb_ctx* ctx) {
     PB_MG_F(PB_BD);
 #undef PB_BD
     CK(cudaGetLastError());
+    M.lines = mg_wants_lines(ctx);
+    if (M.lines) { pb_status st = mg_line_setup(ctx); if (st != PB_OK) return st; }
     // level 0 element matrices E_T = P_T^T S_T P_T of the local cells, Galerkin products below, stencils
     const MgCut C = mg_cut_of(ctx);
     Grid g = ctx->grid;
@@ -133,7 +195,8 @@ static pb_status mg_setup(pb_ctx* ctx) {
         if (it > 0) {
             { pb_status st = spmv_with_halo(ctx, plan, M.wfull, ctx->y, parts + 4 * PCG_MAX_BLOCKS); if (st != PB_OK) return st; }
 #define PB_PW(F_) mg_pow_apply_kernel<F_><<<plan.nblk, PCG_THREADS, 0, sm>>>(nbr, ctx->iAb, ctx->y, w, parts)
-            PB_MG_F(PB_PW);
+            if (M.lines) { mg_line_solve(ctx, ctx->y, w, nullptr); mg_norm2_kernel<<<plan.nblk, PCG_THREADS, 0, sm>>>(n, w, parts); }
+            else PB_MG_F(PB_PW);
 #undef PB_PW
         } else {
             mg_dot_kernel<<<plan.nblk, PCG_THREADS, 0, sm>>>(n, v, v, parts, nullptr, nullptr);      // normalise the start vector
@@ -205,6 +268,15 @@ static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan_d, const double* r, 
     const double lmax = M.lmax, lmin = MG_CHEB_LO * lmax, theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
     const MgCut C = mg_cut_of(ctx);
     auto cheb = [&](int first, int have_y, int acc, int last, double c1, double c2) {
+        if (M.lines) {      // residual update, t = L^{-1} res along the mesh lines, direction update
+#define PB_CH(F_) mg_launch_cheb<F_>(ctx, plan.nblk, nbr, first, have_y, acc, 1, c1, c2, r, rs, w, z)
+            PB_MG_F(PB_CH);
+#undef PB_CH
+            if (last) return;
+            mg_line_solve(ctx, rs, M.tl, ctx->cg);
+            mg_cheb_combine_kernel<<<plan.nblk, PCG_THREADS, 0, sm>>>(n, first, acc, c1, c2, M.tl, w, z, ctx->cg);
+            return;
+        }
 #define PB_CH(F_) mg_launch_cheb<F_>(ctx, plan.nblk, nbr, first, have_y, acc, last, c1, c2, r, rs, w, z)
         PB_MG_F(PB_CH);
 #undef PB_CH

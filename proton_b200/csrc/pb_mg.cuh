@@ -9,8 +9,8 @@
 //                  vertex function to the face monomials: a linear trace is exactly dof0 = mean, dof1 = half the
 //                  difference (face_basis, bases.hpp:241-291: xi = -1 at the sorted first point), higher modes 0.
 //                  On a cut face of the fictitious-domain problem the trace is the linear function through the value
-//                  of the vertex inside the domain and 0 at the intersection point (the Nitsche condition), so
-//                  vertices outside the domain never couple with the inside.  A_0 = P^T A P is formed cell by cell:
+//                  of the vertex inside the domain and 0 at the intersection point (the Nitsche condition), and vertices
+//                  outside the domain carry no coarse unknown at all (mg_face_weights).  A_0 = P^T A P is formed cell by cell:
 //                  E_T = P_T^T S_T P_T (4 x 4 per cell) from the condensed blocks K1/K2 leave in HBM.
 //   levels 1...  : vertices with even indices (the last one kept when N is odd), bilinear interpolation, Galerkin
 //                  operators again as 4 x 4 element matrices per coarse cell, 9-point stencils gathered from them,
@@ -60,6 +60,15 @@ PB_HD void mg_face_weights(const MgCut& C, int F, long long gf, long long pa, lo
         wa[0] = wa[1] = wb[0] = wb[1] = 0.0;
         if (C.node_loc[pa] == PB_IN_NEGATIVE_SIDE) { wa[0] = F == 1 ? 0.5 : xi / (xi + 1.0); wa[1] = -1.0 / (xi + 1.0); }
         else { wb[0] = F == 1 ? 0.5 : -xi / (1.0 - xi); wb[1] = 1.0 / (1.0 - xi); }
+    } else if (C.node_loc) {
+        // vertices outside the domain carry no coarse unknown.  The fictitious-domain system decouples into the inside and the outside
+        // of the interface (a cut cell integrates its inside part only); bilinear interpolation between vertex levels would couple the
+        // two again, and the V-cycle would then excite the smooth modes of the outside problem, which CG has to remove one by one
+        // (measured on the restatement: eigenvalues of M^-1 A down to 0.23 at 48^2, all of them outside modes; tools/scratch/
+        // mg_slow_modes_cut.py).  With zero weights the outside rows and columns of every vertex-level operator vanish (those vertices
+        // keep omega / diagonal = 0), so the outside faces see the smoother only; their right-hand side is zero (cuthho_square.cpp:626-665).
+        if (C.node_loc[pa] != PB_IN_NEGATIVE_SIDE) { wa[0] = 0.0; wa[1] = 0.0; }
+        if (C.node_loc[pb] != PB_IN_NEGATIVE_SIDE) { wb[0] = 0.0; wb[1] = 0.0; }
     }
     if (F == 1) { wa[1] = 0.0; wb[1] = 0.0; }
 }
@@ -422,6 +431,8 @@ struct MgState {
     double lmax = 0.0; double *resfull = nullptr, *zfull = nullptr, *wfull = nullptr, *lam = nullptr;
     long long nfull = 0;
     float* valf = nullptr; long long valf_n = 0;      // fp32 copy of the CSR values (V-cycle SpMVs), or nullptr
+    // line-block Jacobi smoother (pb_mg_lines.cuh): factors of the two line sets (float unless PB_MG_FP64), line-solve output
+    bool lines = false, lines_f64 = false; void *fac_h = nullptr, *fac_v = nullptr; double* tl = nullptr; long long fac_key[3] = {0, 0, 0};
 };
 }  // namespace pb
 #endif

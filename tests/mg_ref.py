@@ -65,6 +65,8 @@ def face_prolongation(m, compress, k, info=None):
                 w = {p0: [0.5 if F == 1 else xi / (xi + 1), -1 / (xi + 1)]}
             else:
                 w = {p1: [0.5 if F == 1 else -xi / (1 - xi), 1 / (1 - xi)]}
+        elif info is not None:               # vertices outside the domain carry no coarse unknown
+            w = {p: c for p, c in w.items() if info["node_loc"][p] == orc.NEG}
         for p, (c0, c1) in w.items():
             rows.append(cf * F); cols.append(p); vals.append(c0)
             if F > 1:
@@ -155,6 +157,25 @@ def block_diag_inverse(Sc, F):
     return lambda r: np.einsum("bac,bc->ba", Binv, r.reshape(nb, F)).ravel()
 
 
+def line_block_inverse(m, compress, Sc, F, row_cuts=None):
+    """r -> L^-1 r, L = the block-tridiagonal parts of Sc along the mesh lines (pb_mg_lines.cuh): columns of horizontal faces (cut at the
+    strip boundaries `row_cuts`, as the ranks of a communicator solve them) and rows of vertical faces"""
+    fpt, fd = m.faces(); N1 = m.Nx + 1
+    line = np.zeros(Sc.shape[0] // F, np.int64)
+    for f in range(m.nfaces):
+        if fd[f]:
+            continue
+        p0, p1 = sorted(fpt[f]); i0, j0 = p0 % N1, p0 // N1
+        if p1 - p0 == 1:                                       # horizontal face h(i0, j0): owned by the strip of cell row j0
+            strip = 0 if row_cuts is None else int(np.searchsorted(row_cuts, j0, side="right"))
+            line[compress[f]] = i0 + N1 * strip
+        else:
+            line[compress[f]] = -1 - j0
+    ld = np.repeat(line, F); A = Sc.tocoo(); keep = ld[A.row] == ld[A.col]
+    lu = spla.splu(sp.csc_matrix((A.data[keep], (A.row[keep], A.col[keep])), shape=Sc.shape))
+    return lu.solve
+
+
 def power_lmax(Sc, Dinv, its=14):
     """the device's estimate: fixed hashed start vector, `its` steps of v <- D^-1 A v / |.|"""
     n = Sc.shape[0]
@@ -170,12 +191,12 @@ def power_lmax(Sc, Dinv, its=14):
 class Preconditioner:
     """z = M^-1 r exactly as mg_apply composes it"""
 
-    def __init__(self, m, S, Sc, k, info=None, nu=2, lmax=None):
+    def __init__(self, m, S, Sc, k, info=None, nu=2, lmax=None, lines=False, row_cuts=None):
         self.A = Sc.tocsr(); self.F = k + 1; self.nu = nu
         self.P = face_prolongation(m, S.compress, k, info)
         self.h = Hierarchy(self.P.T @ self.A @ self.P, m.Nx, m.Ny)
         self.mask = interior_mask(m.Nx, m.Ny).astype(float)
-        self.Dinv = block_diag_inverse(self.A, self.F)
+        self.Dinv = line_block_inverse(m, S.compress, self.A, self.F, row_cuts) if lines else block_diag_inverse(self.A, self.F)
         self.lmax = power_lmax(self.A, self.Dinv) if lmax is None else lmax
 
     def _cheb(self, rhs, x):

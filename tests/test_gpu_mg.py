@@ -42,7 +42,8 @@ def test_hierarchy_and_apply_match_restatement(Nx, Ny, k, cut, values, monkeypat
     m, S, Sc, g = mg_ref.condensed_system(Nx, k, cut=cut, Ny=Ny)
     info = m.cut_info() if cut else None
     nlev, lmax, _ = ctx.mg_info()
-    ref = mg_ref.Preconditioner(m, S, Sc, k, info, nu=1 if cut else 2, lmax=lmax)      # the library's default sweeps per problem
+    # the library's defaults per problem: fictitious domain = 1 Chebyshev step on the LINE-block Jacobi (pb_mg_lines.cuh), plain = 2 steps on the face blocks
+    ref = mg_ref.Preconditioner(m, S, Sc, k, info, nu=1 if cut else 2, lmax=lmax, lines=cut)
     assert nlev == len(ref.h.levels)
     assert abs(lmax - mg_ref.power_lmax(ref.A, ref.Dinv)) < 1e-6 * lmax      # same start vector, same iteration
     for l in range(nlev):
@@ -105,6 +106,41 @@ def test_iterations_do_not_grow_with_the_mesh(k):
         assert r["exit_reason"] == PB.CG_CONVERGED
         its.append(r["iterations"]); ctx.close()
     assert max(its) <= min(its) + 3 and max(its) <= 20, its
+
+
+def test_line_smoother_on_the_area_scaled_stabilisations(monkeypatch):
+    """naive / cut stabilisation (scaled by 1/area): with the face-block smoother the count grows like sqrt(N) (modes that are
+    constant along a mesh line and alternate from line to line); the line-block Jacobi of pb_mg_lines.cuh, the default there, removes
+    them.  Same solution either way."""
+    hdi = pb.hho_degree_info(2, 1)
+    counts = {}
+    for lines in ("1", "0"):
+        monkeypatch.setenv("PB_MG_LINES", lines)
+        for N in (64, 256):
+            ctx = pb.Context(0)
+            ctx.mesh(pb.mesh_init_params(N, N)).assemble(hdi, stab_kind=PB.STAB_NAIVE, fun=PB.FUN_TANH)
+            r = ctx.conjugated_gradient(pb.cg_params(1e-12, 1e8, 1000, 3))
+            assert r["exit_reason"] == PB.CG_CONVERGED
+            counts[(lines, N)] = (r["iterations"], ctx.face_solution()); ctx.close()
+    monkeypatch.delenv("PB_MG_LINES")
+    for N in (64, 256):
+        a, b = counts[("1", N)][1], counts[("0", N)][1]
+        assert np.linalg.norm(a - b) < 1e-8 * np.linalg.norm(b)
+    its = {k: v[0] for k, v in counts.items()}
+    assert its[("1", 256)] <= its[("1", 64)] + 3, its                       # flat with the lines
+    assert its[("0", 256)] >= its[("0", 64)] + 4 and its[("1", 256)] < its[("0", 256)], its
+    # the default on the fictitious-domain problem is the line smoother: far fewer iterations than the face-block smoother
+    res = {}
+    for lines in (None, "0"):
+        if lines is None: monkeypatch.delenv("PB_MG_LINES", raising=False)
+        else: monkeypatch.setenv("PB_MG_LINES", lines)
+        ctx = gpu_system(256, 256, 1, True)
+        r = ctx.conjugated_gradient(pb.cg_params(1e-9, 1e8, 1000, 3))
+        assert r["exit_reason"] == PB.CG_CONVERGED
+        res[lines] = (r["iterations"], ctx.face_solution()); ctx.close()
+    monkeypatch.delenv("PB_MG_LINES", raising=False)
+    assert res[None][0] <= 18 and res[None][0] < 0.7 * res["0"][0], (res[None][0], res["0"][0])
+    assert np.linalg.norm(res[None][1] - res["0"][1]) < 1e-6 * np.linalg.norm(res["0"][1])      # both solved to 1e-9 only
 
 
 def test_rebuilds_after_reassembly_and_other_degree():

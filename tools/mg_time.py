@@ -20,8 +20,8 @@ else:
     ctx.assemble(hdi, fun=PB.FUN_TANH if "tanh" in sys.argv else PB.FUN_SINSIN)
 nl, lmax, setup = ctx.mg_info()
 print(f"N={N} k={k} cut={cut}: unknowns {ctx.n_rows}, mg levels {nl}, lmax {lmax:.3f}, setup {setup:.2f} ms", flush=True)
-for nu in ([1, 2, 3] if "sweep" in sys.argv else [2]):
-    os.environ["PB_MG_NU"] = str(nu)
+for nu in ([1, 2, 3] if "sweep" in sys.argv else ["default"]):
+    if nu != "default": os.environ["PB_MG_NU"] = str(nu)
     for rep in range(2):
         r = ctx.conjugated_gradient(pb.cg_params(tol, 1e8, 5000, 3))
     t = ctx.timings()["ms_pcg"]
