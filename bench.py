@@ -224,6 +224,9 @@ def cut_record(args, rank, world, dev, dist, torch, pb, PB, fp64_peak):
                       "exit_reason": r_mg["exit_reason"], "relative_residual": r_mg["relative_residual"], "solve_ms": solve_ms, "solve_ms_first": solve_first_ms,
                       "solve_note": "solve_ms: hierarchy set-up + iterations, wall clock between barriers, max over ranks; solve_ms_first additionally holds the one-off NCCL connection set-up",
                       "mg_levels": nlev, "smoother_lmax": lmax,
+                      "smoother": ("1 Chebyshev step on the line-block Jacobi (block Thomas along columns of horizontal / rows of vertical faces, pb_mg_lines.cuh)" if world == 1
+                                   else "1 Chebyshev step on the face-block Jacobi (several ranks: the line solve of the strips' full-length rows does not pay, DESIGN 4a)")
+                                  + "; vertices outside the domain carry no coarse unknown",
                       "h1_error": h1, "tight": {"tol": 1e-12, "iterations": r_mg2["iterations"], "exit_reason": r_mg2["exit_reason"], "h1_error": h1_tight,
                                                 "h1_rel_diff": abs(h1 - h1_tight) / h1_tight}},
             "pcg_ms_per_iter": it_ms, "pcg_hbm_frac": iter_bytes / (it_ms * 1e-3) / 1e9 / hbm, "pcg_note": "the reference's Jacobi-PCG, 100 fixed iterations",
@@ -508,7 +511,7 @@ def run_ours(args, rank, world, local_rank):
     cg["multigrid"] = {"tol": 1e-12, "iterations": r_mg["iterations"], "exit_reason": r_mg["exit_reason"], "relative_residual": r_mg["relative_residual"],
                        "solve_ms_with_setup": t_mg_first, "solve_ms": t_mg, "levels": nlev, "smoother_lmax": lmax,
                        "l2_error": math.sqrt(abs(e_mg[0])), "energy_error": math.sqrt(abs(e_mg[2])),
-                       "note": "apply_preconditioner=3: Chebyshev/block-Jacobi smoothing on the face system + Galerkin vertex levels; wall clock between barriers, max over ranks; "
+                       "note": "apply_preconditioner=3: one Chebyshev step per sweep on the face-block Jacobi of the face system + Galerkin vertex levels; wall clock between barriers, max over ranks; "
                                "solve_ms_with_setup = the first solve (hierarchy set-up and, on several GPUs, NCCL's one-off connection set-up), solve_ms = a second solve on the cached hierarchy"}
 
     # ---------------- reduce over ranks (max time), print on rank 0

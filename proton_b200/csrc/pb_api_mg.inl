@@ -84,12 +84,14 @@ template <int F> static void mg_launch_cheb(pb_ctx* ctx, int nblk, long long nbr
                                             const double* src, double* res, double* d, double* z) {
     mg_cheb_kernel<F><<<nblk, PCG_THREADS, 0, ctx->stream>>>(nbr, first, have_y, acc, last, c1, c2, ctx->iAb, src, ctx->y, res, d, z, ctx->cg);
 }
-// line-block Jacobi (pb_mg_lines.cuh): the problems whose stabilisation is scaled by 1/area (naive and cut stabilisation);
-// PB_MG_LINES=0 / 1 overrides
+// line-block Jacobi (pb_mg_lines.cuh): the problems whose stabilisation is scaled by 1/area (naive and cut stabilisation), on
+// single-rank contexts.  On several ranks the face-block smoother is the default: the rows of vertical faces of a strip keep their full
+// length, so the line solve does not get cheaper with the number of ranks while everything else does (BASELINE target on 8 GPUs: 41 iterations
+// x 5.6 ms with the lines against 60 x 3.1 ms without, profiles/r3c_mg_dist8*.txt; one GPU: 36 x 24.3 against 60 x 16.8).  PB_MG_LINES=0 / 1 overrides.
 static bool mg_wants_lines(const pb_ctx* ctx) {
     const char* e = getenv("PB_MG_LINES");
     if (e) return atoi(e) != 0;
-    return ctx->prm.problem == PB_PROBLEM_FICTDOM || ctx->prm.stab_kind != PB_STAB_FANCY;
+    return ctx->world == 1 && (ctx->prm.problem == PB_PROBLEM_FICTDOM || ctx->prm.stab_kind != PB_STAB_FANCY);
 }
 template <int F, typename VT> static void mg_launch_line_factor(pb_ctx* ctx, const MgLineSet& H, const MgLineSet& V) {
     MgState& M = ctx->mg; const long long row0 = ctx->strip.cf_begin * F;

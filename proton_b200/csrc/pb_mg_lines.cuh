@@ -34,6 +34,12 @@ struct MgLineSet {          // the lines of one direction on the owned block row
     long long fac_ls, fac_ss; int warp_per_line;
 };
 PB_HD long long mg_line_fac(const MgLineSet& S, int line, int step) { return (long long)line * S.fac_ls + (long long)step * S.fac_ss; }
+// element e (< 2 F^2) of block (line, step).  One thread per line: structure of arrays, [step][e][line], so that every load of a warp is one
+// 128-byte line (the array-of-blocks layout cost 18 wavefronts per 4-byte load: 3.5 ms per solve at 4096^2).  One warp per line: the blocks of a
+// line are contiguous, [line][step][e], and a chunk of 32 steps is copied linearly.
+PB_HD long long mg_line_fac_elem(const MgLineSet& S, int FF2, int line, int step, int e) {
+    return S.warp_per_line ? ((long long)line * S.nsteps + step) * FF2 + e : ((long long)step * FF2 + e) * S.nlines + line;
+}
 PB_HD long long mg_line_block_row(const MgLineSet& S, int line, int step) {
     if (S.kind == 0) return S.base + (long long)step * S.per + (line ? 2 * line - 1 : 0);
     if (S.row0_first && line == 0) return step;
@@ -107,11 +113,13 @@ __global__ void mg_line_gather_kernel(MgLineSet S, long long row0, const long lo
         mg_csr_block<F>(rowptr, col, val, br, row0 + br * F, D);
         bool have_u = false;
         if (k + 1 < S.nsteps) have_u = mg_csr_block<F>(rowptr, col, val, br, row0 + mg_line_block_row(S, line, k + 1) * F, U);
-        VT* o = fac + mg_line_fac(S, line, k) * (2 * F * F);
 #pragma unroll
         for (int a = 0; a < F; a++)
 #pragma unroll
-            for (int c = 0; c < F; c++) { o[a * F + c] = (VT)D[a][c]; o[F * F + a * F + c] = (VT)(have_u ? U[a][c] : 0.0); }
+            for (int c = 0; c < F; c++) {
+                fac[mg_line_fac_elem(S, 2 * F * F, line, k, a * F + c)] = (VT)D[a][c];
+                fac[mg_line_fac_elem(S, 2 * F * F, line, k, F * F + a * F + c)] = (VT)(have_u ? U[a][c] : 0.0);
+            }
     }
 }
 // factorisation, phase 2 (one thread per line): D_k, U_k -> Sinv_k, G_k in place
@@ -120,8 +128,9 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
     constexpr int CH = MgLineChunk<F>::value, FF = F * F;
     const int line = blockIdx.x * blockDim.x + threadIdx.x;
     if (line >= S.nlines) return;
-    const long long fstride = S.fac_ss * (2 * FF);
-    fac += (long long)line * S.fac_ls * (2 * FF);
+    // element e of step k of this line: fac[k * fstride + e * estride]
+    const long long fstride = S.warp_per_line ? 2 * FF : (long long)(2 * FF) * S.nlines, estride = S.warp_per_line ? 1 : S.nlines;
+    fac += S.warp_per_line ? (long long)line * S.nsteps * (2 * FF) : line;
     double G[F][F], Uprev[F][F];
 #pragma unroll
     for (int a = 0; a < F; a++)
@@ -133,7 +142,7 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
         for (int q = 0; q < CH; q++) {
             const VT* f = fac + (long long)min(k0 + q, S.nsteps - 1) * fstride;
 #pragma unroll
-            for (int e = 0; e < 2 * FF; e++) raw[q][e] = f[e];
+            for (int e = 0; e < 2 * FF; e++) raw[q][e] = f[e * estride];
         }
 #pragma unroll
         for (int q = 0; q < CH; q++) {
@@ -162,7 +171,7 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
 #pragma unroll
                     for (int e = 0; e < F; e++) s += Si[a][e] * (double)raw[q][FF + e * F + c];
                     G[a][c] = s;
-                    o[a * F + c] = (VT)(0.5 * (Si[a][c] + Si[c][a])); o[FF + a * F + c] = (VT)s;
+                    o[(a * F + c) * estride] = (VT)(0.5 * (Si[a][c] + Si[c][a])); o[(FF + a * F + c) * estride] = (VT)s;
                 }
 #pragma unroll
             for (int a = 0; a < F; a++)
@@ -176,8 +185,8 @@ __global__ void mg_line_factor_kernel(MgLineSet S, VT* __restrict__ fac) {
 template <int F, typename VT>
 __device__ __forceinline__ void mg_line_solve_thread(const MgLineSet& S, const VT* __restrict__ fac, const double* __restrict__ r, double* __restrict__ t, int line) {
     constexpr int CH = MgLineChunk<F>::value, FF = F * F;
-    fac += (long long)line * S.fac_ls * (2 * FF);
-    const long long fstride = S.fac_ss * (2 * FF);
+    const long long fstride = (long long)(2 * FF) * S.nlines, estride = S.nlines;      // structure of arrays: [step][e][line]
+    fac += line;
     const int m = S.nsteps;
     // forward: y_k = r_k - G_{k-1}^T y_{k-1};  t_k = Sinv_k y_k
     double y[F], gp[FF];      // y_{k-1}, G_{k-1}
@@ -193,7 +202,7 @@ __device__ __forceinline__ void mg_line_solve_thread(const MgLineSet& S, const V
             e0[q] = mg_line_block_row(S, line, k) * F;
             const VT* fk = fac + (long long)k * fstride;
 #pragma unroll
-            for (int e = 0; e < 2 * FF; e++) f[q][e] = fk[e];
+            for (int e = 0; e < 2 * FF; e++) f[q][e] = fk[e * estride];
 #pragma unroll
             for (int a = 0; a < F; a++) rr[q][a] = r[e0[q] + a];
         }
@@ -231,9 +240,9 @@ __device__ __forceinline__ void mg_line_solve_thread(const MgLineSet& S, const V
         for (int q = 0; q < CH; q++) {
             const int k = max(k1 - q, 0);
             e0[q] = mg_line_block_row(S, line, k) * F;
-            const VT* fk = fac + (long long)k * fstride + FF;
+            const VT* fk = fac + (long long)k * fstride + FF * estride;
 #pragma unroll
-            for (int e = 0; e < FF; e++) g[q][e] = fk[e];
+            for (int e = 0; e < FF; e++) g[q][e] = fk[e * estride];
 #pragma unroll
             for (int a = 0; a < F; a++) tt[q][a] = t[e0[q] + a];
         }
@@ -254,62 +263,64 @@ __device__ __forceinline__ void mg_line_solve_thread(const MgLineSet& S, const V
     }
 }
 
-// the same on one line by one WARP (few long lines): every lane fetches the operands of one step of the next chunk of 32 while lane 0
-// runs the recurrence of the current chunk out of shared memory; results leave through shared memory, one step per lane
-template <int F, typename VT> struct MgLineWarpSmem { VT f[32][2 * F * F]; double r[32][F]; double o[32][F]; };
+// the same on one line by one WARP (few long lines).  Per chunk of 32 steps: the chunk's factor blocks are one contiguous piece, copied with
+// coalesced loads (issued a chunk ahead, in flight during the recurrence) and widened to double on the way into shared memory; lane 0 runs the
+// bare recurrence (y_k = r_k - G_{k-1}^T y_{k-1}, resp. x_k = t_k - G_k x_{k+1}: 9 multiply-adds per step at k = 2), unrolled so that its
+// shared-memory loads run ahead; the products t_k = Sinv_k y_k are then taken by all lanes, one step each.
+template <int F, typename VT> struct MgLineWarpSmem { double f[32][2 * F * F]; double r[32][F]; double o[32][F]; };
 template <int F, typename VT>
 __device__ __forceinline__ void mg_line_solve_warp(const MgLineSet& S, const VT* __restrict__ fac, const double* __restrict__ r, double* __restrict__ t, int line,
                                                    MgLineWarpSmem<F, VT>& sm) {
-    constexpr int FF = F * F;
+    constexpr int FF = F * F, W = 2 * FF;      // words of a block; a chunk = 32 W consecutive words = W loads per lane
     const int lane = threadIdx.x & 31, m = S.nsteps, nch = (m + 31) / 32;
-    fac += (long long)line * S.fac_ls * (2 * FF);
-    const long long fstride = S.fac_ss * (2 * FF);
-    VT nf[2 * FF]; double nr[F];
-    auto fetch_fwd = [&](int c) {
-        const int k = min(c * 32 + lane, m - 1);
-        const VT* fk = fac + (long long)k * fstride;
+    fac += (long long)line * m * W;
+    const long long nwords = (long long)m * W;
+    VT nf[W]; double nr[F];
+    double* const sf = &sm.f[0][0];
+    auto fetch = [&](int k_first, int k_mine, const double* vec) {      // words of the 32 blocks from k_first on; vector entries of step k_mine
+        const long long w0 = (long long)k_first * W;
 #pragma unroll
-        for (int e = 0; e < 2 * FF; e++) nf[e] = fk[e];
-        const long long e0 = mg_line_block_row(S, line, k) * F;
+        for (int j = 0; j < W; j++) { const long long w = w0 + j * 32 + lane; nf[j] = fac[w < nwords ? w : nwords - 1]; }
+        const long long e0 = mg_line_block_row(S, line, k_mine) * F;
 #pragma unroll
-        for (int a = 0; a < F; a++) nr[a] = r[e0 + a];
+        for (int a = 0; a < F; a++) nr[a] = vec[e0 + a];
     };
+    auto stage = [&]() {
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < W; j++) sf[j * 32 + lane] = (double)nf[j];
+#pragma unroll
+        for (int a = 0; a < F; a++) sm.r[lane][a] = nr[a];
+        __syncwarp();
+    };
+    // ---- forward
     double y[F], gp[FF];
 #pragma unroll
     for (int a = 0; a < F; a++) y[a] = 0.0;
 #pragma unroll
     for (int e = 0; e < FF; e++) gp[e] = 0.0;
-    fetch_fwd(0);
+    fetch(0, min(lane, m - 1), r);
     for (int c = 0; c < nch; c++) {
-        __syncwarp();
-#pragma unroll
-        for (int e = 0; e < 2 * FF; e++) sm.f[lane][e] = nf[e];
-#pragma unroll
-        for (int a = 0; a < F; a++) sm.r[lane][a] = nr[a];
-        __syncwarp();
-        if (c + 1 < nch) fetch_fwd(c + 1);                 // in flight during the recurrence below
+        stage();
+        if (c + 1 < nch) fetch((c + 1) * 32, min((c + 1) * 32 + lane, m - 1), r);
+        const int cnt = min(32, m - c * 32);
         if (lane == 0) {
-            const int cnt = min(32, m - c * 32);
-            for (int q = 0; q < cnt; q++) {
-                double yn[F];
+#pragma unroll 8
+            for (int q = 0; q < 32; q++) {
+                if (q < cnt) {
+                    double yn[F];
 #pragma unroll
-                for (int a = 0; a < F; a++) {
-                    double s2 = sm.r[q][a];
+                    for (int a = 0; a < F; a++) {
+                        double s2 = sm.r[q][a];
 #pragma unroll
-                    for (int e = 0; e < F; e++) s2 -= gp[e * F + a] * y[e];
-                    yn[a] = s2;
+                        for (int e = 0; e < F; e++) s2 -= gp[e * F + a] * y[e];
+                        yn[a] = s2;
+                    }
+#pragma unroll
+                    for (int a = 0; a < F; a++) { y[a] = yn[a]; sm.o[q][a] = yn[a]; }
+#pragma unroll
+                    for (int e = 0; e < FF; e++) gp[e] = sm.f[q][FF + e];
                 }
-#pragma unroll
-                for (int a = 0; a < F; a++) y[a] = yn[a];
-#pragma unroll
-                for (int a = 0; a < F; a++) {
-                    double s2 = 0.0;
-#pragma unroll
-                    for (int e = 0; e < F; e++) s2 += (double)sm.f[q][a * F + e] * y[e];
-                    sm.o[q][a] = s2;
-                }
-#pragma unroll
-                for (int e = 0; e < FF; e++) gp[e] = (double)sm.f[q][FF + e];
             }
         }
         __syncwarp();
@@ -317,49 +328,45 @@ __device__ __forceinline__ void mg_line_solve_warp(const MgLineSet& S, const VT*
         if (k < m) {
             const long long e0 = mg_line_block_row(S, line, k) * F;
 #pragma unroll
-            for (int a = 0; a < F; a++) t[e0 + a] = sm.o[lane][a];
+            for (int a = 0; a < F; a++) {
+                double s2 = 0.0;
+#pragma unroll
+                for (int e = 0; e < F; e++) s2 += sm.f[lane][a * F + e] * sm.o[lane][e];
+                t[e0 + a] = s2;
+            }
         }
     }
     __syncwarp();
-    // backward: chunk c holds the steps m-1-32c ... descending, lane = position in the chunk
-    auto fetch_bwd = [&](int c) {
-        const int k = max(m - 1 - c * 32 - lane, 0);
-        const VT* fk = fac + (long long)k * fstride + FF;
-#pragma unroll
-        for (int e = 0; e < FF; e++) nf[e] = fk[e];
-        const long long e0 = mg_line_block_row(S, line, k) * F;
-#pragma unroll
-        for (int a = 0; a < F; a++) nr[a] = t[e0 + a];
-    };
+    // ---- backward: chunk c holds the steps [kb, kb + 32), kb = m - 32 (c + 1) (the last chunk starts below 0: its first -kb slots are idle)
     double x[F];
 #pragma unroll
     for (int a = 0; a < F; a++) x[a] = 0.0;
-    fetch_bwd(0);
+    auto fetch_b = [&](int c) { const int kb = m - 32 * (c + 1); fetch(max(kb, 0), min(max(kb + lane, 0), m - 1), t); };
+    fetch_b(0);
     for (int c = 0; c < nch; c++) {
-        __syncwarp();
-#pragma unroll
-        for (int e = 0; e < FF; e++) sm.f[lane][e] = nf[e];
-#pragma unroll
-        for (int a = 0; a < F; a++) sm.r[lane][a] = nr[a];
-        __syncwarp();
-        if (c + 1 < nch) fetch_bwd(c + 1);
+        const int kb = m - 32 * (c + 1), shift = kb < 0 ? -kb : 0;      // slot q of the staged chunk = step max(kb, 0) + q for the factors ...
+        stage();                                                        // ... and step kb + lane for the vector (clamped)
+        if (c + 1 < nch) fetch_b(c + 1);
         if (lane == 0) {
-            const int cnt = min(32, m - c * 32);
-            for (int q = 0; q < cnt; q++) {
-                double xn[F];
+#pragma unroll 8
+            for (int q = 31; q >= 0; q--) {
+                const int k = kb + q;
+                if (k >= 0) {
+                    double xn[F];
 #pragma unroll
-                for (int a = 0; a < F; a++) {
-                    double s2 = sm.r[q][a];
+                    for (int a = 0; a < F; a++) {
+                        double s2 = sm.r[q][a];
 #pragma unroll
-                    for (int e = 0; e < F; e++) s2 -= (double)sm.f[q][a * F + e] * x[e];
-                    xn[a] = s2;
+                        for (int e = 0; e < F; e++) s2 -= sm.f[q - shift][FF + a * F + e] * x[e];
+                        xn[a] = s2;
+                    }
+#pragma unroll
+                    for (int a = 0; a < F; a++) { x[a] = xn[a]; sm.o[q][a] = xn[a]; }
                 }
-#pragma unroll
-                for (int a = 0; a < F; a++) { x[a] = xn[a]; sm.o[q][a] = xn[a]; }
             }
         }
         __syncwarp();
-        const int k = m - 1 - c * 32 - lane;
+        const int k = kb + lane;
         if (k >= 0) {
             const long long e0 = mg_line_block_row(S, line, k) * F;
 #pragma unroll

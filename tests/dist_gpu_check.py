@@ -98,6 +98,17 @@ def main():
         if not okm:
             print(f"rank {rank}: multigrid fictdom solve differs (N={N} k={k}): {rm}", flush=True)
         ok = ok and okm
+        # the line smoother (default on one rank only) forced on the strips: columns of horizontal faces cut at the strip boundaries
+        os.environ["PB_MG_LINES"] = "1"
+        ctx.assemble(hdi, stab_kind=PB.STAB_CUT, problem=PB.PROBLEM_FICTDOM)          # new values generation: the hierarchy is rebuilt
+        rl = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 5000, 3))
+        del os.environ["PB_MG_LINES"]
+        okl = rl["exit_reason"] == PB.CG_CONVERGED and global_close(ctx.face_solution(), faces) and rl["iterations"] <= rm["iterations"] + 2
+        if rank == 0:
+            print(f"fictdom N={N} k={k} world={world} multigrid, line smoother on strips: iterations {rl['iterations']} (face-block smoother: {rm['iterations']})", flush=True)
+        if not okl:
+            print(f"rank {rank}: line-smoother solve on strips differs (N={N} k={k}): {rl}", flush=True)
+        ok = ok and okl
         ctx.close()
     # two-material interface problem (doubled unknowns on cut faces): every strip owns the contiguous slots of its faces; the cut
     # faces of the strips below are all-reduced inside pb_assemble; halos are slot ranges; H1 error summed over the ranks
