@@ -444,7 +444,11 @@ static pb_status launch_scatter_tile(pb_ctx* ctx) {
     }
     int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, ctx->device);
     const long long ntiles = (ctx->nrows_blk + T - 1) / T;
-    const long long grid = std::min<long long>(ntiles, (long long)nsm * bps * 4);      // a few waves: tiles are short
+    // several waves: tiles are short.  The wave count hardly matters (2.05 ms with one wave, 2.02 with four, 1.99 with eight at 2048^2, k = 2:
+    // profiles/r3h_k3_waves.txt) — in particular a single persistent wave, which would keep the two uses of a cell's block (the face rows below
+    // and above it) close in time, does not lower the time: the L2 miss rate is not what limits K3.  PB_K3_WAVES overrides.
+    static const int waves = getenv("PB_K3_WAVES") ? std::max(1, atoi(getenv("PB_K3_WAVES"))) : 8;
+    const long long grid = std::min<long long>(ntiles, (long long)nsm * bps * waves);
     kern<<<(unsigned)(grid < 1 ? 1 : grid), 256, smem, ctx->stream>>>(ctx->nrows_blk, ctx->brows, ctx->brp, ctx->S, ctx->g, ctx->val, ctx->rhs);
     return PB_OK;
 }
