@@ -2,6 +2,7 @@
 // preconditioner's transfer operators, Galerkin products and stencil assembly) on host arrays, so that tests/test_mg_cpu.py can
 // check it against scipy's P^T A P without a GPU.  The library itself has no host path; nothing here is linked into it.
 #include "../proton_b200/csrc/pb_mg.cuh"
+#include "../proton_b200/csrc/pb_mg_lines.cuh"
 using namespace pb;
 
 static MgGrid whole(int Nx, int Ny) {
@@ -61,6 +62,21 @@ void mgh_face_prolong(int Nx, int Ny, int F, const double* x0, const int* node_l
     for (long long cf = 0; cf < nfree; cf++) {
         double o[2]; mg_face_prolong(g, C, F, L0, x0, cf, o);
         for (int a = 0; a < F; a++) z[cf * F + a] = a < 2 ? o[a] : 0.0;
+    }
+}
+// line sets of the strip of cell rows [rb, re) (pb_mg_lines.cuh): owner[local block row] = kind * 2^40 + line * 2^20 + step for every (line, step),
+// hits[local block row] counts how many (line, step) pairs map to it; dims = { nlines_h, nsteps_h, nlines_v, nsteps_v, warp_per_line_h, warp_per_line_v }
+void mgh_line_sets(int Nx, int Ny, int rb, int re, long long* owner, int* hits, int* dims) {
+    Grid g = grid_of(Nx, Ny);
+    const long long cf_begin = rb == 0 ? 0 : compress_row_start(g, rb);
+    MgLineSet H, V; mg_line_sets(g, rb, re, cf_begin, H, V);
+    dims[0] = H.nlines; dims[1] = H.nsteps; dims[2] = V.nlines; dims[3] = V.nsteps; dims[4] = H.warp_per_line; dims[5] = V.warp_per_line;
+    for (int kind = 0; kind < 2; kind++) {
+        const MgLineSet& S = kind ? V : H;
+        for (int line = 0; line < S.nlines; line++) for (int step = 0; step < S.nsteps; step++) {
+            const long long br = mg_line_block_row(S, line, step);
+            owner[br] = ((long long)kind << 40) + ((long long)line << 20) + step; hits[br]++;
+        }
     }
 }
 }

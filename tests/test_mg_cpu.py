@@ -20,7 +20,8 @@ def H():
     src = os.path.join(HERE, "mg_host_check.cu"); out = os.path.join(HERE, "build", "libmg_host_check.so")
     hdr = os.path.join(HERE, "..", "proton_b200", "csrc", "pb_mg.cuh")
     os.makedirs(os.path.dirname(out), exist_ok=True)
-    if not os.path.exists(out) or max(os.path.getmtime(src), os.path.getmtime(hdr)) > os.path.getmtime(out):
+    hdr2 = os.path.join(HERE, "..", "proton_b200", "csrc", "pb_mg_lines.cuh")
+    if not os.path.exists(out) or max(os.path.getmtime(src), os.path.getmtime(hdr), os.path.getmtime(hdr2)) > os.path.getmtime(out):
         subprocess.check_call(["nvcc", "-O1", "-std=c++17", "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets", "-Xcompiler", "-fPIC", "-shared", "-o", out, src])
     return C.CDLL(out)
 
@@ -155,3 +156,28 @@ def test_restated_preconditioner_gives_flat_iteration_counts(k, cut, N):
         its.append(it)
         assert it < itj / 3
     assert its[1] <= its[0] + (8 if cut else 2), its
+
+
+@pytest.mark.parametrize("Nx,Ny,rb,re", [(6, 5, 0, 5), (7, 9, 0, 4), (7, 9, 4, 7), (7, 9, 7, 9), (5, 6, 2, 3), (3, 3, 0, 1), (300, 40, 10, 30), (2, 2, 0, 2)])
+def test_mesh_lines_cover_the_owned_faces_once(H, Nx, Ny, rb, re):
+    """the line sets of the line-block Jacobi smoother (pb_mg_lines.cuh): every owned free face lies on exactly one line, at the step that
+    the closed-form numbering says: columns of horizontal faces h(i, j) (line i, step j - j0), rows of vertical faces v(i, j) (line j - rb, step i - 1)"""
+    per = 2 * Nx - 1
+    row_start = lambda j: 0 if j == 0 else (Nx - 1) + (j - 1) * per
+    cf_begin = row_start(rb); cf_end = row_start(re) if re < Ny else (Nx - 1) + (Ny - 1) * per
+    n = cf_end - cf_begin
+    owner = np.full(n, -1, np.int64); hits = np.zeros(n, np.int32); dims = np.zeros(6, np.int32)
+    H.mgh_line_sets(Nx, Ny, rb, re, p(owner, C.c_longlong), p(hits, C.c_int), p(dims, C.c_int))
+    assert np.all(hits == 1)
+    j0 = max(rb, 1)
+    assert tuple(dims[:4]) == (Nx, max(re - j0, 0), re - rb, Nx - 1)
+    for j in range(rb, re):
+        for i in range(Nx):
+            if j >= 1:        # h(i, j): compress_h
+                br = row_start(j) + (0 if i == 0 else 2 * i - 1) - cf_begin
+                assert owner[br] == (0 << 40) + (i << 20) + (j - j0)
+            if i >= 1:        # v(i, j): compress_v
+                br = (i - 1 if j == 0 else row_start(j) + 2 * i) - cf_begin
+                assert owner[br] == (1 << 40) + ((j - rb) << 20) + (i - 1)
+    # few long lines go to the warp-per-line solve
+    assert dims[5] == (1 if (re - rb < 2048 and Nx - 1 >= 256) else 0)
