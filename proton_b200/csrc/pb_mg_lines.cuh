@@ -17,8 +17,9 @@
 // vertical faces; its columns of horizontal faces end at the strip (the segments of a column on different ranks are solved
 // independently: block Jacobi between strips, 16 against 14 iterations at 8 strips of 256^2 on the restatement).
 // Block Thomas factorisation per line, S_1 = D_1, S_k = D_k - U_{k-1}^T S_{k-1}^{-1} U_{k-1}: stored are Sinv_k = S_k^{-1} and
-// G_k = S_k^{-1} U_k (the transposed multiplier is G^T because S is symmetric), step-major ([step][line][2][F*F]) so that the threads
-// of a warp, one line each, read consecutive blocks.  Solve: y_k = r_k - G_{k-1}^T y_{k-1}, t_k = Sinv_k y_k, x_k = t_k - G_k x_{k+1}.
+// G_k = S_k^{-1} U_k (the transposed multiplier is G^T because S is symmetric), as a structure of arrays [step][entry][line] so that every
+// load of a warp, one line per thread, is one 128-byte line (sets of few long lines: [line][step][entry], one warp per line).
+// Solve: y_k = r_k - G_{k-1}^T y_{k-1}, t_k = Sinv_k y_k, x_k = t_k - G_k x_{k+1}.
 #pragma once
 #include "pb_mg.cuh"
 
@@ -29,11 +30,8 @@ struct MgLineSet {          // the lines of one direction on the owned block row
     int kind;               // 0: columns of horizontal faces (line = i, step = j - j0); 1: rows of vertical faces (line = j - row_begin, step = i - 1)
     long long base, per;    // closed-form numbering (compress_h / compress_v, pb_device.cuh): see mg_line_block_row
     int row0_first;         // kind 1: line 0 is cell row 0, whose vertical faces are numbered densely from 0
-    // layout of the factor array: block (line, step) at (line * fac_ls + step * fac_ss) * 2 F^2.  Step-major (fac_ls = 1) for one thread
-    // per line (the threads of a warp read consecutive blocks), line-major (fac_ss = 1) for one warp per line (mg_line_solve_warp)
-    long long fac_ls, fac_ss; int warp_per_line;
+    int warp_per_line;      // 1: one warp per line (few long lines), line-major factors; 0: one thread per line, structure-of-arrays factors (mg_line_fac_elem)
 };
-PB_HD long long mg_line_fac(const MgLineSet& S, int line, int step) { return (long long)line * S.fac_ls + (long long)step * S.fac_ss; }
 // element e (< 2 F^2) of block (line, step).  One thread per line: structure of arrays, [step][e][line], so that every load of a warp is one
 // 128-byte line (the array-of-blocks layout cost 18 wavefronts per 4-byte load: 3.5 ms per solve at 4096^2).  One warp per line: the blocks of a
 // line are contiguous, [line][step][e], and a chunk of 32 steps is copied linearly.
@@ -53,10 +51,7 @@ PB_HD void mg_line_sets(const Grid& g, long long row_begin, long long row_end, l
     V.kind = 1; V.nlines = (int)(row_end - row_begin); V.nsteps = (int)(g.Nx - 1); V.per = per; V.row0_first = row_begin == 0 ? 1 : 0;
     V.base = (row_begin == 0 ? (g.Nx - 1) - per : compress_row_start(g, row_begin)) - cf_begin;
     // few long lines (the rows of vertical faces of a narrow strip: their length does not shrink with the number of ranks): one warp per line
-    for (MgLineSet* S : {&H, &V}) {
-        S->warp_per_line = (S->nlines < 2048 && S->nsteps >= 256) ? 1 : 0;
-        if (S->warp_per_line) { S->fac_ls = S->nsteps; S->fac_ss = 1; } else { S->fac_ls = 1; S->fac_ss = S->nlines; }
-    }
+    for (MgLineSet* S : {&H, &V}) S->warp_per_line = (S->nlines < 2048 && S->nsteps >= 256) ? 1 : 0;
 }
 
 #ifdef __CUDACC__
