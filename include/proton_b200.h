@@ -172,7 +172,9 @@ pb_status pb_strip_layout(long long Nx, long long Ny, long long row_begin, long 
 pb_status pb_dist_unique_id(unsigned char id[128]);
 pb_status pb_dist_init(pb_ctx* ctx, int rank, int world, const unsigned char id[128]);
 /* back-substitution on a strip: cell dofs of the OWNED cell rows only ([row_begin,row_end) x Nx x cbs) and the owned
- * face dofs */
+ * face dofs.  Interface problem: the cell part is interface_assembler's packed layout of the owned cells, (owned cells + owned cut
+ * cells, pb_cut_counts) x cbs with a cut cell's negative set followed by its positive one; the ranks' cell parts, then their face parts,
+ * concatenated in rank order are the vector of pb_recover */
 pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
 
 /* ---- two-material interface problem, `cuthho_square -i` (PB_PROBLEM_INTERFACE).  pb_assemble replaces the
@@ -188,7 +190,8 @@ pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
  * contexts WITHOUT one (several strips driven by one process) are told: pb_interface_cut_faces_owned after the cut preprocessing,
  * the host's prefix sum, pb_interface_set_cut_offsets(before, total) before pb_assemble.  pb_interface_strip_layout: out =
  * { first owned slot, one past the last, first / one-past-last referenced slot, slots of the whole system, block rows the lower /
- * the upper neighbour reads of this strip }.  pb_recover, pb_sample_solution and pb_interface_get_local stay whole-mesh calls;
+ * the upper neighbour reads of this strip }.  pb_recover_strip returns the strip's part of the reference's vector; pb_recover,
+ * pb_sample_solution and pb_interface_get_local stay whole-mesh calls;
  * pb_interface_face_table reports the faces outside the strip's window as -2.
  * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems.  pb_recover returns interface_assembler's solution
  * layout: (ncells + ncut) cell blocks of cbs in cell_table order (a cut cell carries its negative, then its positive set,

@@ -181,8 +181,12 @@ class Context:
         self.rank, self.world = rank, world
 
     def recover_strip(self, row_begin, row_end):
-        """(cell dofs of the owned cell rows, owned face dofs)"""
-        cells = np.zeros((row_end - row_begin) * self.mip.Nx * self.hdi.cbs); faces = np.zeros(self.n_rows)
+        """(cell dofs of the owned cell rows, owned face dofs).  Interface problem: the cell part is interface_assembler's packed layout of
+        the owned cells (a cut cell carries its negative, then its positive set); the ranks' parts concatenate to the vector of recover()"""
+        ncell = (row_end - row_begin) * self.mip.Nx
+        if getattr(self, "problem", None) == PB.PROBLEM_INTERFACE:
+            ncell += self.cut_counts_owned()[1]
+        cells = np.zeros(ncell * self.hdi.cbs); faces = np.zeros(self.n_rows)
         self._ck(lib().pb_recover_strip(self._h, _ptr(cells), _ptr(faces)))
         return cells, faces
 

@@ -248,6 +248,7 @@ static pb_status launch_spmv(pb_ctx* ctx, const SpmvPlan& P, const double* vfull
 }
 
 static pb_status pcg_multigrid(pb_ctx* ctx, const pb_cg_params* p, pb_cg_result* res);      // pb_api_mg.inl
+static pb_status interface_recover_owned(pb_ctx* ctx, double* cell_dofs, double* face_dofs);      // pb_api_interface_post.inl
 
 // conjugated_gradient (solver_cg.hpp:63-144) on the condensed system of this context, or of the row of contexts that
 // share a communicator: same update order, exit tests and iteration count; dot products are all-reduced.
@@ -396,8 +397,8 @@ static pb_status recover_owned(pb_ctx* ctx, double* cell_dofs_host, double** kee
 extern "C" pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs) {
     if (!ctx) return PB_ERR_INVALID;
     NEED(ctx->assembled && ctx->x && cell_dofs, PB_ERR_STATE, "pb_recover_strip: no face solution");
-    NEED(!ctx->general_csr, PB_ERR_UNSUPPORTED, "pb_recover_strip: whole-mesh pb_recover only for the interface problem");
     CK(cudaSetDevice(ctx->device));
+    if (ctx->general_csr) return interface_recover_owned(ctx, cell_dofs, face_dofs);      // (owned cells + owned cut cells) * cbs cell dofs
     pb_status st = recover_owned(ctx, cell_dofs); if (st != PB_OK) return st;
     if (face_dofs) CK(cudaMemcpy(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost));
     return PB_OK;

@@ -29,13 +29,14 @@ __global__ void ifc_recover_cut_kernel(Grid g, int F, int C, int slot0, int ncut
         ucut[t] = v;
     }
 }
-__global__ void ifc_pack_cells_kernel(Grid g, int C, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ cell_loc,
+// cells [c_begin, c_end) = the owned cells, slot0 = first owned slot of the cut-cell list: the packed layout starts at the first owned cell
+// (uc by global cell id through a shifted pointer, ucut by slot of the window list)
+__global__ void ifc_pack_cells_kernel(Grid g, int C, long long c_begin, long long c_end, int slot0, int ncut, const int* __restrict__ cut_cells, const int* __restrict__ cell_loc,
                                       const double* __restrict__ uc, const double* __restrict__ ucut, double* __restrict__ out) {
-    const long long nc = g.Nx * g.Ny;
-    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < nc; c += (long long)gridDim.x * blockDim.x) {
-        int lo = 0, hi = ncut;                      // cut cells before c = cell_table[c] - c
+    for (long long c = c_begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; c < c_end; c += (long long)gridDim.x * blockDim.x) {
+        int lo = slot0, hi = ncut;                  // cut cells before c = cell_table[c] - c
         while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
-        double* o = out + (c + lo) * C;
+        double* o = out + ((c - c_begin) + (lo - slot0)) * C;
         if (cell_loc[c] == PB_ON_INTERFACE) for (int a = 0; a < 2 * C; a++) o[a] = ucut[(long long)lo * 2 * C + a];
         else for (int a = 0; a < C; a++) o[a] = uc[c * C + a];
     }
@@ -266,22 +267,31 @@ static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** 
     return PB_OK;
 }
 
-static pb_status interface_recover(pb_ctx* ctx, double* full) {
-    NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED,
-         "pb_recover (interface): the reference's full vector is assembled on whole-mesh contexts (strips: pb_error_norms, pb_get_face_solution)");
+// the owned part of the reference's solution vector: cell blocks of the owned cells in cell_table order (a cut cell carries its negative, then
+// its positive set), (owned cells + owned cut cells) * cbs doubles, and the owned face unknowns.  The ranks' parts, concatenated in rank
+// order (cells, then faces), are the whole-mesh vector.
+static pb_status interface_recover_owned(pb_ctx* ctx, double* cell_dofs, double* face_dofs) {
     const Grid& g = ctx->grid; const int C = ctx->C;
-    const long long nc = g.Nx * g.Ny, ncell_dofs = (nc + ctx->ncut) * C;
+    const long long c_begin = g.row_begin * g.Nx, c_end = g.row_end * g.Nx, ncell_dofs = ((c_end - c_begin) + ctx->ncut_owned) * C;
     double *uc = nullptr, *ucut = nullptr, *packed = nullptr;
     pb_status st = interface_cell_unknowns(ctx, &uc, &ucut); if (st != PB_OK) return st;
-    CK(cudaMalloc((void**)&packed, (size_t)ncell_dofs * 8));
-    ifc_pack_cells_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, C, ctx->ncut, ctx->cut_cells, ctx->cell_loc_g, uc, ucut, packed);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(full, packed, (size_t)ncell_dofs * 8, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(full + ncell_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    cudaError_t e = cudaMalloc((void**)&packed, (size_t)ncell_dofs * 8);
+    if (e == cudaSuccess) {
+        ifc_pack_cells_kernel<<<148 * 8, 256, 0, ctx->stream>>>(g, C, c_begin, c_end, ctx->ncut - ctx->ncut_owned, ctx->ncut, ctx->cut_cells, ctx->cell_loc_g, uc - c_begin * C, ucut, packed);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(cell_dofs, packed, (size_t)ncell_dofs * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && face_dofs) e = cudaMemcpyAsync(face_dofs, ctx->x, (size_t)ctx->nrows * 8, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(uc); cudaFree(ucut); cudaFree(packed);
     if (e != cudaSuccess) return fail(ctx, PB_ERR_CUDA, "pb_recover (interface): %s", cudaGetErrorString(e));
     return PB_OK;
+}
+static pb_status interface_recover(pb_ctx* ctx, double* full) {
+    NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED,
+         "pb_recover (interface): whole-mesh contexts (strips: pb_recover_strip, whose parts concatenate to this vector)");
+    const Grid& g = ctx->grid;
+    return interface_recover_owned(ctx, full, full + (g.Nx * g.Ny + ctx->ncut) * ctx->C);
 }
 
 static pb_status interface_error(pb_ctx* ctx, double out[3]) {

@@ -121,8 +121,9 @@ def main():
         res = ctx.conjugated_gradient(pb.cg_params(1e-13, 1e8, 200000, True))
         faces = ctx.face_solution()
         et = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{lr}"); dist.all_reduce(et)
-        gf = [None] * world; gl = [None] * world
-        dist.all_gather_object(gf, faces); dist.all_gather_object(gl, (L["slot_begin"], L["slot_end"], L["slots"]))
+        cells_s, faces_s = ctx.recover_strip(ctx.row_begin, ctx.row_end)          # the strip's part of the reference's packed solution vector
+        gf = [None] * world; gl = [None] * world; gcs = [None] * world
+        dist.all_gather_object(gf, faces); dist.all_gather_object(gl, (L["slot_begin"], L["slot_end"], L["slots"])); dist.all_gather_object(gcs, cells_s)
         if rank == 0:
             ref = pb.Context(lr)
             ref.mesh(mip, PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
@@ -132,9 +133,11 @@ def main():
             got = np.concatenate(gf)
             contiguous = gl[0][0] == 0 and all(gl[i][1] == gl[i + 1][0] for i in range(world - 1)) and gl[-1][1] == gl[-1][2] == ref.n_rows // hdi.fbs
             err = np.linalg.norm(got - x1) / np.linalg.norm(x1) if got.shape == x1.shape else float("inf")
+            full1 = ref.recover(); fullN = np.concatenate(gcs + gf)              # cells of all ranks, then faces of all ranks = pb_recover's layout
+            errf = np.linalg.norm(fullN - full1) / np.linalg.norm(full1) if fullN.shape == full1.shape else float("inf")
             print(f"interface N={N} k={k} world={world}: unknowns {ref.n_rows}, iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, "
-                  f"rel diff {err:.2e}, H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
-            ok = ok and contiguous and err < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2 and abs(float(et[0]) - e1) <= 1e-8 * e1
+                  f"rel diff {err:.2e} (recover_strip parts against pb_recover: {errf:.2e}), H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
+            ok = ok and contiguous and err < 1e-8 and errf < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2 and abs(float(et[0]) - e1) <= 1e-8 * e1
             ref.close()
         ctx.close()
     flag = torch.tensor([1 if ok else 0], device=f"cuda:{lr}")
