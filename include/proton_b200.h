@@ -190,8 +190,9 @@ pb_status pb_recover_strip(pb_ctx* ctx, double* cell_dofs, double* face_dofs);
  * contexts WITHOUT one (several strips driven by one process) are told: pb_interface_cut_faces_owned after the cut preprocessing,
  * the host's prefix sum, pb_interface_set_cut_offsets(before, total) before pb_assemble.  pb_interface_strip_layout: out =
  * { first owned slot, one past the last, first / one-past-last referenced slot, slots of the whole system, block rows the lower /
- * the upper neighbour reads of this strip }.  pb_recover_strip returns the strip's part of the reference's vector; pb_recover,
- * pb_sample_solution and pb_interface_get_local stay whole-mesh calls;
+ * the upper neighbour reads of this strip }.  pb_recover_strip returns the strip's part of the reference's vector, pb_sample_solution the rows
+ * of interface_uT.dat of the owned cells (the ranks of a communicator call these together: they fetch the halo of the solution); pb_recover and
+ * pb_interface_get_local stay whole-mesh calls;
  * pb_interface_face_table reports the faces outside the strip's window as -2.
  * pb_get_csr / pb_pcg / pb_get_face_solution work as for the other problems.  pb_recover returns interface_assembler's solution
  * layout: (ncells + ncut) cell blocks of cbs in cell_table order (a cut cell carries its negative, then its positive set,

@@ -134,16 +134,18 @@ static pb_status interface_cell_unknowns(pb_ctx* ctx, double** uc_out, double** 
 template <int CD>
 __global__ void __launch_bounds__(32) interface_sample_kernel(Grid g, const double2* __restrict__ points, const int* __restrict__ node_loc,
                                                                const int* __restrict__ cell_loc, const int* __restrict__ cut_cells, const double2* __restrict__ iface,
-                                                               int ncut, int NI, const double* __restrict__ uc, const double* __restrict__ ucut, double* __restrict__ out) {
+                                                               int ncut, int NI, long long c_begin, long long c_end, int slot0, const double* __restrict__ uc,
+                                                               const double* __restrict__ ucut, double* __restrict__ out) {
+    // (cells [c_begin, c_end) = the owned cells, slot0 = the first owned slot of the cut-cell list: the rows start at the first owned cell;
+    //  uc by global cell id through a shifted pointer)
     constexpr int C = cell_basis_size(CD);
     constexpr int nq0 = cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * CD);
     __shared__ double tp[2 * CUT_MAX_TP];
     __shared__ int s_ntp;
     const int lane = threadIdx.x;
-    const long long nc = g.Nx * g.Ny;
     const int ri = dunavant_rule_index(2 * CD), np = c_qt.dun_n[ri];
     const long long ncutq = (long long)(4 + 2 * NI) * np;
-    for (long long c = blockIdx.x; c < nc; c += gridDim.x) {
+    for (long long c = c_begin + blockIdx.x; c < c_end; c += gridDim.x) {
         const long long ci = c % g.Nx, cj = c / g.Nx, p0 = grid_point(g, ci, cj);
         const long long pid[4] = {p0, p0 + 1, p0 + g.Nx + 2, p0 + g.Nx + 1};
         CellGeom geo; int nloc[4];
@@ -151,9 +153,9 @@ __global__ void __launch_bounds__(32) interface_sample_kernel(Grid g, const doub
         for (int i = 0; i < 4; i++) { const double2 v = points[pid[i]]; geo.vx[i] = v.x; geo.vy[i] = v.y; nloc[i] = node_loc[pid[i]]; }
         cell_geometry(geo);
         const double ih = geo.ihalf;
-        int lo = 0, hi = ncut;                      // cut cells before c
+        int lo = slot0, hi = ncut;                  // cut cells before c
         while (lo < hi) { const int mid = (lo + hi) / 2; if (cut_cells[mid] < c) lo = mid + 1; else hi = mid; }
-        double* o = out + 3 * ((c - lo) * nq0 + lo * ncutq);
+        double* o = out + 3 * (((c - c_begin) - (lo - slot0)) * nq0 + (lo - slot0) * ncutq);
         auto emit = [&](const double* u, long long idx, double x, double y) {
             double phi[C], dx[C], dy[C];
             eval_cell_basis<CD>((x - geo.barx) * ih, (y - geo.bary) * ih, ih, phi, dx, dy);
@@ -210,13 +212,12 @@ __global__ void __launch_bounds__(32) interface_sample_kernel(Grid g, const doub
     }
 }
 
-static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {
-    NEED(ctx->world == 1 && ctx->strip.cf_begin == 0 && ctx->strip.cf_end == num_free_faces(ctx->grid), PB_ERR_UNSUPPORTED, "pb_sample_solution (interface): whole-mesh contexts");
+static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_points, long long* n_points) {      // rows of the OWNED cells
     const Grid& g = ctx->grid; const int CD = ctx->CD;
-    const long long nc = g.Nx * g.Ny;
-    const int np = dunavant_npts(2 * CD);
+    const long long c_begin = g.row_begin * g.Nx, c_end = g.row_end * g.Nx, nc = c_end - c_begin;
+    const int np = dunavant_npts(2 * CD), slot0 = ctx->ncut - ctx->ncut_owned;
     const long long nq0 = cell_qps(PB_QUAD_POLY_DUNAVANT, 2 * CD), ncutq = (long long)(4 + 2 * ctx->NI) * np;
-    const long long total = (nc - ctx->ncut) * nq0 + (long long)ctx->ncut * ncutq;
+    const long long total = (nc - ctx->ncut_owned) * nq0 + (long long)ctx->ncut_owned * ncutq;
     *n_points = total;
     if (!xyv) return PB_OK;
     NEED(capacity_points >= total, PB_ERR_INVALID, "pb_sample_solution: buffer too small");
@@ -224,7 +225,8 @@ static pb_status interface_sample(pb_ctx* ctx, double* xyv, long long capacity_p
     pb_status st = interface_cell_unknowns(ctx, &uc, &ucut); if (st != PB_OK) return st;
     CK(cudaMalloc((void**)&out, (size_t)total * 24));
     const int grid = (int)std::min<long long>(nc, 148 * 32);
-#define PB_SMP(CD_) interface_sample_kernel<CD_><<<grid, 32, 0, ctx->stream>>>(g, ctx->points, ctx->node_loc, ctx->cell_loc_g, ctx->cut_cells, ctx->iface, ctx->ncut, ctx->NI, uc, ucut, out)
+#define PB_SMP(CD_) interface_sample_kernel<CD_><<<grid, 32, 0, ctx->stream>>>(g, ctx->points, ctx->node_loc, ctx->cell_loc_g, ctx->cut_cells, ctx->iface, ctx->ncut, ctx->NI, \
+                                                                              c_begin, c_end, slot0, uc - c_begin * ctx->C, ucut, out)
     switch (CD) { case 1: PB_SMP(1); break; case 2: PB_SMP(2); break; default: PB_SMP(3); break; }
 #undef PB_SMP
     cudaError_t e = cudaGetLastError();

@@ -122,8 +122,10 @@ def main():
         faces = ctx.face_solution()
         et = torch.tensor([ctx.error_norms()[0]], dtype=torch.float64, device=f"cuda:{lr}"); dist.all_reduce(et)
         cells_s, faces_s = ctx.recover_strip(ctx.row_begin, ctx.row_end)          # the strip's part of the reference's packed solution vector
-        gf = [None] * world; gl = [None] * world; gcs = [None] * world
+        rows_s = ctx.sample_solution()                                             # the strip's rows of interface_uT.dat
+        gf = [None] * world; gl = [None] * world; gcs = [None] * world; grs = [None] * world
         dist.all_gather_object(gf, faces); dist.all_gather_object(gl, (L["slot_begin"], L["slot_end"], L["slots"])); dist.all_gather_object(gcs, cells_s)
+        dist.all_gather_object(grs, rows_s)
         if rank == 0:
             ref = pb.Context(lr)
             ref.mesh(mip, PB.QUAD_POLY_DUNAVANT); ref.cut_levelset(0, 0.35, 0.5, 0.5); ref.cut_preprocess(4)
@@ -135,6 +137,9 @@ def main():
             err = np.linalg.norm(got - x1) / np.linalg.norm(x1) if got.shape == x1.shape else float("inf")
             full1 = ref.recover(); fullN = np.concatenate(gcs + gf)              # cells of all ranks, then faces of all ranks = pb_recover's layout
             errf = np.linalg.norm(fullN - full1) / np.linalg.norm(full1) if fullN.shape == full1.shape else float("inf")
+            rows1 = ref.sample_solution(); rowsN = np.concatenate(grs)           # interface_uT.dat: same points bit for bit, same values to the solve
+            same_rows = rowsN.shape == rows1.shape and np.array_equal(rowsN[:, :2], rows1[:, :2]) and np.abs(rowsN[:, 2] - rows1[:, 2]).max() <= 1e-10 * np.abs(rows1[:, 2]).max()
+            errf = errf if same_rows else float("inf")
             print(f"interface N={N} k={k} world={world}: unknowns {ref.n_rows}, iterations {res['iterations']} (1 GPU: {r1['iterations']}), exit {res['exit_reason']}, "
                   f"rel diff {err:.2e} (recover_strip parts against pb_recover: {errf:.2e}), H1^2 {float(et[0]):.12e} (1 GPU: {e1:.12e})", flush=True)
             ok = ok and contiguous and err < 1e-8 and errf < 1e-8 and res["exit_reason"] == PB.CG_CONVERGED and abs(res["iterations"] - r1["iterations"]) <= 2 and abs(float(et[0]) - e1) <= 1e-8 * e1
