@@ -105,8 +105,9 @@ template <int F, typename VT> static void mg_launch_line_factor(pb_ctx* ctx, con
 // tl = L^{-1} r (owned rows)
 template <int F, typename VT> static void mg_launch_line_solve(pb_ctx* ctx, const MgLineSet& H, const MgLineSet& V, const double* r, double* t, const CgState* st) {
     MgState& M = ctx->mg;
-    const int nbA = mg_line_blocks(H), nbB = mg_line_blocks(V);
-    if (nbA + nbB > 0) mg_line_solve_kernel<F, VT><<<nbA + nbB, 128, 0, ctx->stream>>>(H, (const VT*)M.fac_h, nbA, V, (const VT*)M.fac_v, r, t, st);
+    static const int lanes = [] { const char* e = getenv("PB_MG_LINE_LANES"); const int v = e ? atoi(e) : 16; return v >= 32 ? 32 : v >= 16 ? 16 : v >= 8 ? 8 : 4; }();
+    const int nbA = mg_line_blocks(H, lanes), nbB = mg_line_blocks(V, lanes);
+    if (nbA + nbB > 0) mg_line_solve_kernel<F, VT><<<nbA + nbB, 32, 0, ctx->stream>>>(H, (const VT*)M.fac_h, nbA, V, (const VT*)M.fac_v, lanes, r, t, st);
 }
 static void mg_line_solve(pb_ctx* ctx, const double* r, double* t, const CgState* st) {
     MgLineSet H, V; mg_line_sets(ctx->grid, ctx->grid.row_begin, ctx->grid.row_end, ctx->strip.cf_begin, H, V);

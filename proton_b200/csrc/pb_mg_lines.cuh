@@ -370,24 +370,25 @@ __device__ __forceinline__ void mg_line_solve_warp(const MgLineSet& S, const VT*
     }
 }
 
-// t = L^{-1} r on the lines of both directions in one launch of 128-thread blocks: blocks [0, nbA) serve set A, the rest set B; each set
-// by one thread or one warp per line (MgLineSet::warp_per_line).  r, t = owned rows.
-PB_HD int mg_line_blocks(const MgLineSet& S) { if (S.nlines <= 0 || S.nsteps <= 0) return 0; return S.warp_per_line ? (S.nlines + 3) / 4 : (S.nlines + 127) / 128; }
+// t = L^{-1} r on the lines of both directions in one launch of one-warp blocks: blocks [0, nbA) serve set A, the rest set B; each set by one
+// thread or one warp per line (MgLineSet::warp_per_line).  One thread per line: only `lanes` lanes of a warp carry a line, so that the few
+// thousand lines of a mesh spread over all SMs as independent instruction streams (8192 lines in full 128-thread blocks occupy 64 of the
+// 148 SMs).  r, t = owned rows.
+PB_HD int mg_line_blocks(const MgLineSet& S, int lanes) { if (S.nlines <= 0 || S.nsteps <= 0) return 0; return S.warp_per_line ? S.nlines : (S.nlines + lanes - 1) / lanes; }
 template <int F, typename VT>
-__global__ void __launch_bounds__(128) mg_line_solve_kernel(MgLineSet A, const VT* __restrict__ facA, int nbA, MgLineSet B, const VT* __restrict__ facB,
-                                                            const double* __restrict__ r, double* __restrict__ t, const CgState* st) {
-    __shared__ MgLineWarpSmem<F, VT> sm[4];
+__global__ void __launch_bounds__(32) mg_line_solve_kernel(MgLineSet A, const VT* __restrict__ facA, int nbA, MgLineSet B, const VT* __restrict__ facB, int lanes,
+                                                           const double* __restrict__ r, double* __restrict__ t, const CgState* st) {
+    __shared__ MgLineWarpSmem<F, VT> sm;
     if (st && st->done) return;
     const bool second = (int)blockIdx.x >= nbA;
     const MgLineSet S = second ? B : A;
     const VT* __restrict__ fac = second ? facB : facA;
     const int blk = second ? blockIdx.x - nbA : blockIdx.x;
     if (S.warp_per_line) {
-        const int line = blk * 4 + (threadIdx.x >> 5);
-        if (line < S.nlines) mg_line_solve_warp<F, VT>(S, fac, r, t, line, sm[threadIdx.x >> 5]);
+        if (blk < S.nlines) mg_line_solve_warp<F, VT>(S, fac, r, t, blk, sm);
     } else {
-        const int line = blk * 128 + threadIdx.x;
-        if (line < S.nlines) mg_line_solve_thread<F, VT>(S, fac, r, t, line);
+        const int line = blk * lanes + threadIdx.x;
+        if ((int)threadIdx.x < lanes && line < S.nlines) mg_line_solve_thread<F, VT>(S, fac, r, t, line);
     }
 }
 
