@@ -1,0 +1,26 @@
+"""The reference arm of bench.py (`--impl reference`: the oracle's restatement of the reference's assembly loop on the host cores) runs without
+a GPU; this holds its JSON line to the driver's contract.  (The GPU arm is run by the driver and by tools/scratch/final1.sh.)"""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_reference_arm_prints_the_contract_line():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1                                   # ONE json line
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "HHO cells assembled+condensed/sec" and d["unit"] == "cells/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] == 1 and d["vs_baseline"] is None
+    assert d["value"] > 0 and d["ms_per_step"] > 0 and d["dtype"] == "f64" and d["data"] == "synthetic"
+    assert "workload" in d["config"] and "model" not in d["config"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # the linear setFromTriplets restatement is the timed finalize; the sort-based one of round 1 is reported beside it
+    assert cb["sort_based_value"] > 0 and "setFromTriplets" in cb["finalize"]
