@@ -94,7 +94,8 @@ __device__ __forceinline__ void mg_invert_spd(double A[F][F], double B[F][F]) { 
 
 // steps whose operands a thread loads ahead of the recurrence (all loads of a chunk are independent of it and in flight together;
 // without the staging every step waited for its own DRAM round trip: 8.5 ms per solve at 4096^2 against 0.9 ms)
-template <int F> struct MgLineChunk { static constexpr int value = F <= 2 ? 16 : F == 3 ? 8 : 6; };
+// (k = 1: 16 steps with 24 bytes of spills measured 4.29 ms per iteration at 2048^2 against 4.40 with 12 and none; k = 3: 4 steps, no spills)
+template <int F> struct MgLineChunk { static constexpr int value = F <= 2 ? 16 : F == 3 ? 8 : 4; };
 
 // factorisation, phase 1 (one thread per step of a line): the raw blocks D_k and U_k into the slots of Sinv_k and G_k
 template <int F, typename VT>
