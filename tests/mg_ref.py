@@ -11,13 +11,15 @@ from oracle import orc
 CHEB_LO, OMEGA = 0.15, 0.8
 
 
-def condensed_system(N, k, cut=False, fun=orc.FUN_SINSIN, Ny=None, radius=0.35, threads=1):
+def condensed_system(N, k, cut=False, fun=orc.FUN_SINSIN, Ny=None, radius=0.35, threads=1, stab=None):
     """(mesh, full System, condensed matrix, condensed rhs): Schur complement of the oracle's full cell+face system"""
     Ny = N if Ny is None else Ny
     m = orc.Mesh(N, Ny, poly=cut)
     if cut:
         m.cut_preprocess(radius=radius, refsteps=4)
         S = m.assemble(k + 1, k, stab=orc.STAB_CUT, problem=1, fun=fun, threads=threads)
+    elif stab is not None:
+        S = m.assemble(k + 1, k, stab=stab, fun=fun, threads=threads)
     else:
         S = m.assemble(k + 1, k, fun=fun, threads=threads)
     A = S.matrix().tocsr(); b = S.rhs

@@ -181,3 +181,20 @@ def test_mesh_lines_cover_the_owned_faces_once(H, Nx, Ny, rb, re):
                 assert owner[br] == (1 << 40) + ((j - rb) << 20) + (i - 1)
     # few long lines go to the warp-per-line solve
     assert dims[5] == (1 if (re - rb < 2048 and Nx - 1 >= 256) else 0)
+
+
+def test_restated_line_smoother_removes_the_growth_on_the_area_scaled_stabilisation():
+    """the method of pb_mg_lines.cuh on the scipy restatement, no GPU: with the naive stabilisation (scaled by 1/area) the
+    face-block smoother leaves modes that are constant along a mesh line and alternate from line to line, and the PCG count grows with N;
+    block-tridiagonal solves along the lines remove them.  Same solution either way."""
+    point, lines = [], []
+    for N in (32, 64, 128):
+        m, S, Sc, g = mg_ref.condensed_system(N, 1, stab=orc.STAB_NAIVE, fun=orc.FUN_TANH, threads=4)
+        xs = []
+        for use_lines, out in ((False, point), (True, lines)):
+            M = mg_ref.Preconditioner(m, S, Sc, 1, None, nu=1, lines=use_lines)
+            x, it, rel = mg_ref.pcg(Sc, g, M, tol=1e-10, maxit=500)
+            out.append(it); xs.append(x)
+        assert np.linalg.norm(xs[0] - xs[1]) <= 1e-7 * np.linalg.norm(xs[1])
+    assert lines[2] <= lines[0] + 2, (point, lines)
+    assert point[2] >= point[0] + 4 and lines[2] < point[2], (point, lines)
